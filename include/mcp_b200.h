@@ -1,0 +1,144 @@
+/* mcp_b200.h -- C ABI of libmcp_b200.so, the sm_100a native layer of mpi_cuda_process_b200.
+ *
+ * Every function returns 0 on success and a negative MCP_ERR_* code on failure; the message is
+ * available from mcp_last_error() (thread-local).  Pointers named *_dev are device pointers of the
+ * current CUDA device; `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *
+ * "Reference" citations name the file:line of Rodrigovicente/MPI-CUDA-Process whose function the
+ * entry point provides (M: = MDF_kernel.cu, K: = kernel.cu).
+ */
+#ifndef MCP_B200_H
+#define MCP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* element kinds */
+#define MCP_DTYPE_F32 0
+#define MCP_DTYPE_F64 1
+#define MCP_DTYPE_I32 2
+
+/* stencil operators */
+#define MCP_OP_MDF 0  /* 2-D 5-point heat/Jacobi update, M:10-22 */
+#define MCP_OP_LIFE 1 /* Game of Life B3/S23, K:10-68 */
+
+/* residual modes of the fused kernel */
+#define MCP_RES_NONE 0
+#define MCP_RES_LAST 1 /* residual of the last generation of every time block */
+
+/* ---- runtime (reference: bring-up/teardown in main(), M:114-144,223-234) ---------------------- */
+const char* mcp_last_error(void);
+int mcp_version(void);
+int mcp_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
+
+/* Symmetric arena: one allocation per rank, zero-filled, shareable with peer processes through
+ * CUDA IPC so that kernels can store straight into a neighbour GPU's ghost rows over NVLink.
+ * Replaces the replicated full-grid cudaMalloc of M:141-144 and the host staging of M:161,171,177. */
+int mcp_arena_alloc(size_t bytes, void** ptr);
+int mcp_arena_free(void* ptr);
+int mcp_ipc_handle_size(void);
+int mcp_ipc_get_handle(void* ptr, void* handle_out);
+int mcp_ipc_open_handle(const void* handle, void** ptr_out);
+int mcp_ipc_close_handle(void* ptr);
+int mcp_enable_peer_access(int peer_device);
+
+/* ---- initialisation and boundary conditions (reference: create_universe, M:88-99, K:131-146) --- */
+/* Fill local rows [0, rows_alloc) of a pitched buffer from the global init rule: global row of local
+ * row r is row0 + r; cells outside the h x w domain (ghost rows of edge ranks, pad columns) are 0. */
+int mcp_init_ring2d(int dtype, void* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double ring,
+                    double interior, void* stream);
+/* Seeded synthetic life field: ring dead, interior alive iff hash32(i*w+j, seed) < prob * 2^32. */
+int mcp_init_life_hash(int32_t* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double prob,
+                       uint32_t seed, void* stream);
+/* Re-impose the fixed ring on owned rows (the "else -> 100 / 0" branches of M:35,43,59,67, K:86,102,110). */
+int mcp_apply_ring2d(int dtype, void* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double ring,
+                     void* stream);
+/* 3-D: boundary shell = ring, interior = interior; local planes/rows offset by (z0, y0). */
+int mcp_init_shell3d(int dtype, void* u_dev, int64_t pitch, int64_t plane_pitch, int planes_alloc, int rows_alloc,
+                     int z0, int y0, int d, int h, int w, double ring, double interior, void* stream);
+
+/* ---- plain one-generation kernels (baseline path; reference: middle_kernel/border_kernel M:24-70, K:70-113) */
+/* Updates local rows [row_lo, row_hi) of `in` into `out`; reads rows row_lo-1 .. row_hi.  Cells with global
+ * row/col outside [ylo,yhi] x [xlo,xhi] keep their value. */
+int mcp_step2d(int op, int dtype, const void* in_dev, void* out_dev, int64_t pitch, int rows_alloc, int row0, int h,
+               int w, int row_lo, int row_hi, int ylo, int yhi, int xlo, int xhi, void* stream);
+/* 3-D 7-point heat step on local planes [z_lo,z_hi) x rows [y_lo,y_hi). */
+int mcp_step3d(int dtype, const void* in_dev, void* out_dev, int64_t pitch, int64_t plane_pitch, int planes_alloc,
+               int rows_alloc, int z0, int y0, int d, int h, int w, int z_lo, int z_hi, int y_lo, int y_hi,
+               double coeff, void* stream);
+
+/* ---- fused halo + stencil (+ residual) persistent kernel -------------------------------------------
+ * One cooperative launch advances `generations` generations: TMA-fed shared-memory row ring per warp,
+ * `time_block` generations per HBM pass held in registers, boundary rows stored straight into the
+ * neighbour GPUs' ghost rows (peer pointers) and signalled with system-scope release counters.
+ * Reference: the whole generation loop M:155-222 (kernels + MPI halo + staging copies). */
+typedef struct mcp_fused2d_desc {
+    int op;          /* MCP_OP_* */
+    int dtype;       /* MCP_DTYPE_* */
+    int h, w;        /* global grid */
+    int row_start;   /* first owned global row */
+    int rows_own;    /* owned rows */
+    int ghost;       /* ghost rows above and below the owned rows in every buffer (>= time_block) */
+    int64_t pitch;   /* elements per row, multiple of 32 */
+    void* buf[2];    /* local double buffer, each (ghost + rows_own + ghost) x pitch */
+    void* up_buf[2]; /* rank-1's buffers mapped into this process, or NULL at the top of the chain */
+    void* dn_buf[2]; /* rank+1's buffers, or NULL at the bottom */
+    int up_rows_own; /* rows owned by rank-1 (locates its bottom ghost rows) */
+    uint64_t* flags;   /* local: [0] arrivals from rank-1, [1] arrivals from rank+1 (8-byte counters, zeroed) */
+    uint64_t* up_flag; /* address of rank-1's flags[1] mapped here, or NULL */
+    uint64_t* dn_flag; /* address of rank+1's flags[0] mapped here, or NULL */
+    int ylo, yhi, xlo, xhi; /* cells outside this inclusive global box keep their value */
+    int chunk_rows;  /* rows per tile (0 = choose) */
+    int max_ctas;    /* 0 = one CTA per SM */
+} mcp_fused2d_desc;
+
+typedef struct mcp_fused2d_plan mcp_fused2d_plan;
+
+int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out);
+/* Advance `generations` generations; the state ends in buffer mcp_fused2d_parity(plan). */
+int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int residual_mode, void* stream);
+int mcp_fused2d_parity(const mcp_fused2d_plan* plan);
+int mcp_fused2d_set_parity(mcp_fused2d_plan* plan, int parity);
+/* Local residual history of the last run with MCP_RES_LAST: per time block (sum of squares, max abs) of
+ * u' - u over this rank's owned cells.  Returns the number of entries written (<= max_entries). */
+int mcp_fused2d_residuals(mcp_fused2d_plan* plan, double* sumsq_max_pairs, int max_entries);
+/* 0 = healthy; otherwise the MCP_ERR_* code a kernel recorded (e.g. halo-flag wait timeout). */
+int mcp_fused2d_status(mcp_fused2d_plan* plan);
+/* Number of kernel launches issued by the plan so far. */
+int64_t mcp_fused2d_launches(const mcp_fused2d_plan* plan);
+int mcp_fused2d_geometry(const mcp_fused2d_plan* plan, int time_block, int* n_strips, int* n_chunks, int* grid,
+                         int* smem_bytes);
+int mcp_fused2d_destroy(mcp_fused2d_plan* plan);
+
+/* ---- residual of two fields (unfused; two-pass, fixed order, deterministic) ------------------------
+ * out_host[0] = sum over the row range of (a-b)^2 in fp64, out_host[1] = max |a-b|.
+ * `scratch_dev` holds at least mcp_residual2d_scratch_bytes() bytes. */
+size_t mcp_residual2d_scratch_bytes(void);
+int mcp_residual2d(int dtype, const void* a_dev, const void* b_dev, int64_t pitch, int w, int row_lo, int row_hi,
+                   void* scratch_dev, double* out_dev, void* stream);
+
+/* ---- gather + pack (reference: print_array, K:115-129; no gather exists in the reference) -------- */
+/* Cast/pack owned rows [row_lo,row_hi) x [0,w) of a pitched buffer into a dense destination (which may be a
+ * peer pointer on rank 0): mode 0 = raw copy, 1 = fp64 -> fp32, 2 = int32 cells -> print_array bytes
+ * ('0' if cell == 1 else ' ', '\n' after each row; dst row stride w+1). */
+int mcp_pack_rows(int dtype, int mode, const void* src_dev, int64_t pitch, int w, int row_lo, int row_hi,
+                  void* dst_dev, int64_t dst_row0, void* stream);
+
+/* ---- CPU reference (host code; works without a GPU) ------------------------------------------------ */
+/* glibc rand() stream exactly as the reference consumes it (K:141-142): fills an h x w int32 grid. */
+int mcp_host_life_init_reference(int32_t* u, int h, int w, float prob);
+/* One generation on the host with the literal mixed-precision arithmetic of M:20 (fp32 adds, fp64 final fma). */
+int mcp_host_mdf_step_f32(const float* in, float* out, int h, int w, int strict_fp64);
+int mcp_host_mdf_step_f64(const double* in, double* out, int h, int w);
+int mcp_host_life_step(const int32_t* in, int32_t* out, int h, int w, int fixed_ring);
+/* print_array (K:115-129) into a byte buffer of size 2 + h*(w+1). Returns bytes written. */
+int64_t mcp_host_print_array(const int32_t* u, int w, int64_t size, char* out, int64_t out_cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCP_B200_H */

@@ -1,0 +1,162 @@
+"""Run interface.
+
+Compatible with the reference's: three prompts on stdout and three integers on stdin -- generations,
+height, width (MDF_kernel.cu:103-112, kernel.cu:150-159):
+
+    echo "100 256 256" | python -m mpi_cuda_process_b200 --workload mdf
+
+The reference reads stdin on *every* rank before MPI_Init (defect D1: under most launchers only rank 0
+has a stdin); here rank 0 prompts and reads, then broadcasts.  Everything else is a flag.  Under
+``torchrun`` the same command runs one rank per GPU.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from typing import List, Optional
+
+PROMPTS = (
+    "Enter desired number of generations:\n",
+    "Enter desired height of universe:\n",
+    "Enter desired width of universe:\n",
+)
+
+
+def read_ghw(stream=None, out=None) -> List[int]:
+    """Print the reference's three prompts and parse three whitespace-separated ints (scanf("%d") semantics)."""
+    stream = stream if stream is not None else sys.stdin
+    out = out if out is not None else sys.stdout
+    vals: List[int] = []
+    pending: List[str] = []
+    for prompt in PROMPTS:
+        out.write(prompt)
+        out.flush()
+        while not pending:
+            line = stream.readline()
+            if line == "":
+                raise EOFError("expected three integers on stdin: generations height width")
+            pending = line.split()
+        vals.append(int(pending.pop(0)))
+    return vals
+
+
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(prog="mpi_cuda_process_b200", description=__doc__.split("\n\n")[0])
+    p.add_argument("--workload", choices=["mdf", "life", "heat3d"], default="mdf")
+    p.add_argument("-g", "--generations", type=int, default=None)
+    p.add_argument("--height", type=int, default=None)
+    p.add_argument("--width", type=int, default=None)
+    p.add_argument("--depth", type=int, default=0)
+    p.add_argument("--dtype", choices=["fp32", "fp64"], default="fp32")
+    p.add_argument("--bc", choices=["fixed-ring", "dead-outside"], default=None)
+    p.add_argument("--backend", choices=["auto", "fused", "nccl", "staged", "cpu"], default="auto")
+    p.add_argument("--decomposition", choices=["slab", "pencil"], default="slab")
+    p.add_argument("--pencil", type=int, nargs=2, default=(0, 0), metavar=("PZ", "PY"))
+    p.add_argument("--time-block", type=int, default=4)
+    p.add_argument("--tol", type=float, default=None, help="run to tolerance on the global residual")
+    p.add_argument("--max-generations", type=int, default=0)
+    p.add_argument("--residual", choices=["none", "l2", "linf"], default="none")
+    p.add_argument("--seed", type=int, default=None)
+    p.add_argument("--prob", type=float, default=0.15)
+    p.add_argument("--ring", type=float, default=100.0)
+    p.add_argument("--interior", type=float, default=0.0)
+    p.add_argument("--halo-message", choices=["row", "element"], default="row")
+    p.add_argument("--strict-fp64-accum", action="store_true")
+    p.add_argument("--output", default=None, help="write the final field here (rank 0)")
+    p.add_argument("--output-format", choices=["ascii", "npy", "raw", "text"], default=None)
+    p.add_argument("--print", dest="print_field", action="store_true",
+                   help="print the final life grid in the reference's print_array format")
+    p.add_argument("--check", action="store_true", help="compare with the CPU oracle (small grids)")
+    p.add_argument("--json", action="store_true", help="print run statistics as one JSON line")
+    p.add_argument("--no-prompt", action="store_true", help="do not read g/h/w from stdin (flags only)")
+    p.add_argument("--checkpoint-dir", default=None)
+    p.add_argument("--checkpoint-every", type=int, default=0)
+    p.add_argument("--resume", default=None, help="checkpoint directory to resume from")
+    return p
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    args = build_parser().parse_args(argv)
+    from .config import RunConfig
+    from .parallel.context import init_context
+    from .solver import Solver
+    from . import io as mio, oracle
+    from .utils import checkpoint as ckpt
+
+    ctx = init_context(device="cpu" if args.backend == "cpu" else None)
+    need_stdin = not args.no_prompt and (args.generations is None or args.height is None or args.width is None)
+    ghw = None
+    if need_stdin:
+        if ctx.rank == 0:
+            ghw = read_ghw()
+        ghw = ctx.broadcast_object(ghw, 0)
+    g = args.generations if args.generations is not None else (ghw[0] if ghw else 1)
+    h = args.height if args.height is not None else (ghw[1] if ghw else 256)
+    w = args.width if args.width is not None else (ghw[2] if ghw else 256)
+
+    cfg = RunConfig(
+        workload=args.workload, generations=g, height=h, width=w, depth=args.depth,
+        dtype="int32" if args.workload == "life" else args.dtype,
+        bc=args.bc or ("dead-outside" if args.workload == "life" else "fixed-ring"),
+        ring=args.ring, interior=args.interior, prob=args.prob, seed=args.seed, backend=args.backend,
+        decomposition=args.decomposition, pencil=tuple(args.pencil), time_block=args.time_block, tol=args.tol,
+        max_generations=args.max_generations, residual=args.residual, halo_message=args.halo_message,
+        output=args.output, output_format=args.output_format or ("ascii" if args.workload == "life" else "npy"),
+        strict_fp64_accum=args.strict_fp64_accum, checkpoint_every=args.checkpoint_every,
+        checkpoint_dir=args.checkpoint_dir)
+
+    rc = 0
+    with Solver(cfg, ctx=ctx) as solver:
+        if args.resume:
+            ckpt.load(solver, args.resume)
+        else:
+            solver.initialize()
+        if cfg.tol is not None:
+            stats = solver.run_to_tolerance()
+        elif cfg.checkpoint_every > 0 and cfg.checkpoint_dir:
+            from .solver import RunStats
+            stats = RunStats(cells=cfg.cells)
+            left = g
+            while left > 0:
+                n = min(cfg.checkpoint_every, left)
+                s = solver.run(n, residual=cfg.residual != "none")
+                stats.generations += n
+                stats.device_ms += s.device_ms
+                stats.launches += s.launches
+                stats.residual_history += s.residual_history
+                left -= n
+                ckpt.save(solver, cfg.checkpoint_dir)
+        else:
+            stats = solver.run(g, residual=cfg.residual != "none")
+        solver.check_status()
+        need_field = bool(args.output or args.print_field or args.check)
+        field = solver.gather() if need_field else None
+        if ctx.rank == 0:
+            if args.print_field and field is not None:
+                mio.print_array(field)
+            if args.output and field is not None:
+                mio.dump_field(field, args.output, cfg.output_format)
+            if args.check and field is not None:
+                ref = oracle.run_field(cfg, oracle.init_field(cfg), solver.generation)
+                same = bool((ref == field).all())
+                print(f"oracle check: {'bitwise equal' if same else 'MISMATCH'} after {solver.generation} generations")
+                rc = 0 if same else 1
+            summary = {
+                "workload": cfg.workload, "backend": solver.backend, "world": ctx.world, "shape": list(cfg.shape),
+                "generations": stats.generations, "device_ms": round(stats.device_ms, 4),
+                "glups": round(stats.glups, 3), "launches": stats.launches,
+                "residual": stats.residual_history[-1][1] if stats.residual_history else None,
+            }
+            if args.json:
+                print(json.dumps(summary))
+            else:
+                print(f"{cfg.workload} {cfg.shape} x {stats.generations} generations on {ctx.world} rank(s) "
+                      f"[{solver.backend}]: {stats.device_ms:.3f} ms, {stats.glups:.2f} GLUPS")
+        rc = ctx.broadcast_object(rc, 0)
+    ctx.close()
+    return rc
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,777 @@
+// Fused halo-exchange + 2-D stencil (+ residual) persistent kernel for sm_100a.
+//
+// What it replaces in the reference: the per-generation sequence of MDF_kernel.cu:155-222 --
+// full-grid H2D copy, middle_kernel, w-2 one-element MPI_Recv, second H2D copy, border_kernel,
+// cudaDeviceSynchronize, full-grid D2H copy, w-2 one-element MPI_Send -- and the kernels
+// run_mdf/middle_kernel/border_kernel (MDF_kernel.cu:10-70), game_of_life (kernel.cu:10-113).
+//
+// Design (B200-first, not a translation):
+//  * One cooperative launch runs many generations.  148 CTAs x 16 warps stay resident.
+//  * The slab is cut into tiles = (column strip of 32 lanes x 16 B) x (row chunk).  A tile belongs to ONE
+//    warp; warps never synchronise with each other inside a sweep.
+//  * Each warp owns a 4-stage shared-memory ring fed by TMA (cp.async.bulk.tensor.2d, 6 rows x 512 B
+//    per stage, mbarrier completion).  TMA's out-of-bounds fill supplies the cells outside the allocation.
+//  * Temporal blocking in registers: a warp streams down the rows and carries TB generations as a
+//    wavefront (3-row window per level, compile-time rotated), so HBM sees one read + one write per
+//    TB generations.  Left/right neighbours come from warp shuffles.  Each update is the reference's
+//    exact rounding sequence, so results are bit-identical to a generation-at-a-time Jacobi.
+//  * Tiles on the slab cut store their top/bottom `ghost` output rows twice: locally and straight into
+//    the neighbour GPU's ghost rows through an NVLink-mapped peer pointer, then bump a system-scope
+//    release counter in the neighbour's flag pad.  Tiles that read ghost rows acquire-spin on their local
+//    counter first.  Boundary tiles are scheduled first so the transfer overlaps the interior tiles.
+//  * Sweeps are separated by a device-side grid barrier (no host round trip, no NCCL, no MPI).
+//  * Optional fused residual: per-tile (sum d^2, max |d|) in fp64 -> fixed-order reduction (deterministic).
+#include <cooperative_groups.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "../../../include/mcp_b200.h"
+#include "common.cuh"
+#include "ptx.cuh"
+#include "stencil_ops.cuh"
+
+namespace mcp {
+
+constexpr int kWarpsPerCta = 16;
+constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kRowsPerStage = 6;  // multiple of 3: the 3-row register window rotates at compile time
+constexpr int kStages = 4;
+constexpr int kRowBytes = 512;  // 32 lanes x 16 B
+constexpr int kStageBytes = kRowsPerStage * kRowBytes;
+constexpr int kSmemBytes = kWarpsPerCta * kStages * kStageBytes + kWarpsPerCta * kStages * 8;
+constexpr int kMaxResSlots = 4096;
+
+struct Fused2dParams {
+    void* buf[2];
+    void* up_buf[2];
+    void* dn_buf[2];
+    const unsigned long long* my_flags;  // [0] arrivals from up, [1] arrivals from down
+    unsigned long long* up_flag;
+    unsigned long long* dn_flag;
+    unsigned long long* grid_bar;
+    int* status;
+    double* partials;  // [2][n_tiles][2]
+    double* res_out;   // [kMaxResSlots][2]
+    unsigned long long flag_base_up, flag_base_dn;
+    unsigned long long bar_base;
+    unsigned long long timeout_ns;
+    long long pitch;
+    int rows_alloc, h, w, row0;
+    int own_lo, own_hi;
+    int ylo, yhi, xlo, xhi;
+    int G, up_ghost_row;
+    int n_strips, n_chunks;
+    int sweeps, first_parity, res_slot0;
+};
+
+// ------------------------------------------------------------------------------------------ operators
+
+struct MdfF32 {
+    using T = float;
+    using V = float4;
+    static constexpr int VEC = 4;
+    struct Row {
+        V v;
+    };
+    static __device__ __forceinline__ Row make_row(const V& raw) { return Row{raw}; }
+    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
+        const float wl = __shfl_up_sync(0xffffffffu, c.v.w, 1);
+        const float er = __shfl_down_sync(0xffffffffu, c.v.x, 1);
+        V o;
+        o.x = mdf_cell(c.v.x, n.v.x, s.v.x, wl, c.v.y);
+        o.y = mdf_cell(c.v.y, n.v.y, s.v.y, c.v.x, c.v.z);
+        o.z = mdf_cell(c.v.z, n.v.z, s.v.z, c.v.y, c.v.w);
+        o.w = mdf_cell(c.v.w, n.v.w, s.v.w, c.v.z, er);
+        return o;
+    }
+    static __device__ __forceinline__ V select(unsigned m, const V& keep, const V& upd) {
+        V o;
+        o.x = (m & 1u) ? keep.x : upd.x;
+        o.y = (m & 2u) ? keep.y : upd.y;
+        o.z = (m & 4u) ? keep.z : upd.z;
+        o.w = (m & 8u) ? keep.w : upd.w;
+        return o;
+    }
+    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
+        const double d0 = (double)a.x - (double)b.x, d1 = (double)a.y - (double)b.y;
+        const double d2 = (double)a.z - (double)b.z, d3 = (double)a.w - (double)b.w;
+        ss = fma(d0, d0, ss); ss = fma(d1, d1, ss); ss = fma(d2, d2, ss); ss = fma(d3, d3, ss);
+        mx = fmax(mx, fmax(fmax(fabs(d0), fabs(d1)), fmax(fabs(d2), fabs(d3))));
+    }
+};
+
+struct MdfF64 {
+    using T = double;
+    using V = double2;
+    static constexpr int VEC = 2;
+    struct Row {
+        V v;
+    };
+    static __device__ __forceinline__ Row make_row(const V& raw) { return Row{raw}; }
+    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
+        const double wl = __shfl_up_sync(0xffffffffu, c.v.y, 1);
+        const double er = __shfl_down_sync(0xffffffffu, c.v.x, 1);
+        V o;
+        o.x = mdf_cell(c.v.x, n.v.x, s.v.x, wl, c.v.y);
+        o.y = mdf_cell(c.v.y, n.v.y, s.v.y, c.v.x, er);
+        return o;
+    }
+    static __device__ __forceinline__ V select(unsigned m, const V& keep, const V& upd) {
+        V o;
+        o.x = (m & 1u) ? keep.x : upd.x;
+        o.y = (m & 2u) ? keep.y : upd.y;
+        return o;
+    }
+    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
+        const double d0 = a.x - b.x, d1 = a.y - b.y;
+        ss = fma(d0, d0, ss); ss = fma(d1, d1, ss);
+        mx = fmax(mx, fmax(fabs(d0), fabs(d1)));
+    }
+};
+
+struct LifeI32 {
+    using T = int;
+    using V = int4;
+    static constexpr int VEC = 4;
+    struct Row {
+        V v;   // cells
+        V hs;  // horizontal 3-sums (left + self + right)
+    };
+    static __device__ __forceinline__ Row make_row(const V& raw) {
+        const int wl = __shfl_up_sync(0xffffffffu, raw.w, 1);
+        const int er = __shfl_down_sync(0xffffffffu, raw.x, 1);
+        Row r;
+        r.v = raw;
+        const int xy = raw.x + raw.y, zw = raw.z + raw.w;
+        r.hs.x = wl + xy;
+        r.hs.y = xy + raw.z;
+        r.hs.z = raw.y + zw;
+        r.hs.w = zw + er;
+        return r;
+    }
+    static __device__ __forceinline__ int rule(int n, int c) { return life_rule(n, c); }
+    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
+        V o;
+        o.x = rule(n.hs.x + s.hs.x + c.hs.x - c.v.x, c.v.x);
+        o.y = rule(n.hs.y + s.hs.y + c.hs.y - c.v.y, c.v.y);
+        o.z = rule(n.hs.z + s.hs.z + c.hs.z - c.v.z, c.v.z);
+        o.w = rule(n.hs.w + s.hs.w + c.hs.w - c.v.w, c.v.w);
+        return o;
+    }
+    static __device__ __forceinline__ V select(unsigned m, const V& keep, const V& upd) {
+        V o;
+        o.x = (m & 1u) ? keep.x : upd.x;
+        o.y = (m & 2u) ? keep.y : upd.y;
+        o.z = (m & 4u) ? keep.z : upd.z;
+        o.w = (m & 8u) ? keep.w : upd.w;
+        return o;
+    }
+    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
+        const int d0 = a.x - b.x, d1 = a.y - b.y, d2 = a.z - b.z, d3 = a.w - b.w;
+        const int q = d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+        ss += (double)q;
+        mx = fmax(mx, q ? 1.0 : 0.0);
+    }
+};
+
+template <class V>
+__device__ __forceinline__ V bitcast_v(const uint4& u) {
+    static_assert(sizeof(V) == 16, "vector must be 16 bytes");
+    V v;
+    memcpy(&v, &u, 16);
+    return v;
+}
+template <class V>
+__device__ __forceinline__ uint4 bitcast_u(const V& v) {
+    uint4 u;
+    memcpy(&u, &v, 16);
+    return u;
+}
+
+__host__ __device__ constexpr int mod3(int x) { return ((x % 3) + 3) % 3; }
+
+// ------------------------------------------------------------------------------------------ waits
+
+__device__ __forceinline__ bool aborted(const Fused2dParams& p) { return *((volatile int*)p.status) != 0; }
+
+// Lane-0 style bounded acquire spin on a monotonic counter.  Returns false on abort/timeout.
+__device__ __noinline__ bool wait_counter_sys(const Fused2dParams& p, const unsigned long long* ctr,
+                                              unsigned long long need) {
+    if (ptx::ld_acquire_sys(ctr) >= need) return true;
+    const unsigned long long t0 = ptx::globaltimer_ns();
+    unsigned spins = 0;
+    while (ptx::ld_acquire_sys(ctr) < need) {
+        if ((++spins & 255u) == 0) {
+            if (aborted(p)) return false;
+            if (ptx::globaltimer_ns() - t0 > p.timeout_ns) {
+                atomicCAS(p.status, 0, MCP_ERR_TIMEOUT);
+                return false;
+            }
+            __nanosleep(64);
+        }
+    }
+    return true;
+}
+
+__device__ __noinline__ void grid_barrier(const Fused2dParams& p, unsigned long long& epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::fence_proxy_async();  // our generic-proxy stores are read by other CTAs' TMA loads next sweep
+        __threadfence();
+        const unsigned long long target = p.bar_base + (epoch + 1ull) * gridDim.x;
+        ptx::red_add_release_gpu(p.grid_bar, 1ull);
+        const unsigned long long t0 = ptx::globaltimer_ns();
+        unsigned spins = 0;
+        while (ptx::ld_acquire_gpu(p.grid_bar) < target) {
+            if ((++spins & 1023u) == 0) {
+                if (aborted(p)) break;
+                if (ptx::globaltimer_ns() - t0 > p.timeout_ns) {
+                    atomicCAS(p.status, 0, MCP_ERR_TIMEOUT);
+                    break;
+                }
+            }
+        }
+        ptx::fence_proxy_async();
+    }
+    __syncthreads();
+    ++epoch;
+}
+
+// ------------------------------------------------------------------------------------------ tile
+
+template <class Op, int TB, bool MASKED, bool RES>
+__device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUtensorMap* tm_in,
+                                             typename Op::T* __restrict__ out, typename Op::T* up_out,
+                                             typename Op::T* dn_out, const int x_ld, const int y0, const int y1,
+                                             uint8_t* my_smem, uint64_t* bars, uint32_t& it, const int lane,
+                                             double& rs, double& rm) {
+    using V = typename Op::V;
+    using Row = typename Op::Row;
+    constexpr int VEC = Op::VEC;
+    constexpr int M = (TB + VEC - 1) / VEC;  // margin lanes whose cells go stale within TB levels
+
+    const int ys = y0 - TB;
+    const int n_in = (y1 - y0) + 2 * TB;
+    const int n_it = (n_in + kRowsPerStage - 1) / kRowsPerStage;
+    const int cx = x_ld + lane * VEC;
+
+    unsigned colfix = 0;
+    if (MASKED) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            const int gx = cx + v;
+            if (gx < p.xlo || gx > p.xhi) colfix |= 1u << v;
+        }
+    }
+    const bool lane_valid = (lane >= M) && (lane < 32 - M);
+    const bool lane_store = lane_valid && (cx < (int)p.pitch);
+    const bool push_up = (up_out != nullptr) && (y0 < p.own_lo + p.G);
+    const bool push_dn = (dn_out != nullptr) && (y1 > p.own_hi - p.G);
+
+    Row L[TB][3];
+#pragma unroll
+    for (int t = 0; t < TB; ++t)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) L[t][k] = Op::make_row(bitcast_v<V>(make_uint4(0, 0, 0, 0)));
+
+    auto issue = [&](uint32_t k, int row) {
+        const uint32_t st = k % kStages;
+        ptx::mbar_arrive_expect_tx(&bars[st], kStageBytes);
+        ptx::tma_load_2d(my_smem + st * kStageBytes, tm_in, &bars[st], x_ld, row);
+    };
+
+    if (lane == 0) {
+        const int npro = n_it < kStages ? n_it : kStages;
+        for (int i = 0; i < npro; ++i) issue(it + i, ys + i * kRowsPerStage);
+    }
+
+    for (int i = 0; i < n_it; ++i) {
+        const uint32_t st = it % kStages, par = (it / kStages) & 1u;
+        ptx::mbar_wait(&bars[st], par);
+        const uint8_t* sp = my_smem + st * kStageBytes + lane * 16;
+        const int cbase = i * kRowsPerStage;
+#pragma unroll
+        for (int j = 0; j < kRowsPerStage; ++j) {
+            const int c = cbase + j;  // input-row counter within the tile; local row = ys + c
+            L[0][mod3(j)] = Op::make_row(bitcast_v<V>(ptx::ld_shared_v4(sp + j * kRowBytes)));
+#pragma unroll
+            for (int t = 1; t <= TB; ++t) {
+                const int sc = mod3(j - t), sn = mod3(j - t - 1), ss = mod3(j - t + 1);
+                V res = Op::update(L[t - 1][sn], L[t - 1][sc], L[t - 1][ss]);
+                if (MASKED) {
+                    const int gy = p.row0 + ys + c - t;
+                    const unsigned m = (gy < p.ylo || gy > p.yhi) ? 0xfu : colfix;
+                    res = Op::select(m, L[t - 1][sc].v, res);
+                }
+                if (t < TB) {
+                    L[t < TB ? t : 0][sc] = Op::make_row(res);
+                } else {
+                    const int r_out = ys + c - TB;
+                    if (r_out >= y0 && r_out < y1) {
+                        if (RES) {
+                            if (lane_valid) Op::accum(res, L[TB - 1][sc].v, rs, rm);
+                        }
+                        if (lane_store) {
+                            const uint4 bits = bitcast_u<V>(res);
+                            ptx::st_global_v4(out + (long long)r_out * p.pitch + cx, bits);
+                            if (push_up && r_out < p.own_lo + p.G)
+                                ptx::st_global_v4(
+                                    up_out + (long long)(p.up_ghost_row + (r_out - p.own_lo)) * p.pitch + cx, bits);
+                            if (push_dn && r_out >= p.own_hi - p.G)
+                                ptx::st_global_v4(dn_out + (long long)(r_out - (p.own_hi - p.G)) * p.pitch + cx,
+                                                  bits);
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0 && i + kStages < n_it) issue(it + kStages, ys + (i + kStages) * kRowsPerStage);
+        ++it;
+    }
+}
+
+template <class Op, int TB, bool RES>
+__global__ void __launch_bounds__(kThreads, 1)
+fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ Fused2dParams p) {
+    using T = typename Op::T;
+    constexpr int VEC = Op::VEC;
+    constexpr int M = (TB + VEC - 1) / VEC;
+    constexpr int OUTW = (32 - 2 * M) * VEC;
+
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t* my_smem = smem + warp * (kStages * kStageBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWarpsPerCta * kStages * kStageBytes) + warp * kStages;
+    __shared__ double red_ss[kThreads / 32], red_mx[kThreads / 32];
+
+    if (lane == 0) {
+        for (int s = 0; s < kStages; ++s) ptx::mbar_init(&bars[s], 1);
+        ptx::mbar_fence_init();
+        ptx::prefetch_tensormap(&tmA);
+        ptx::prefetch_tensormap(&tmB);
+    }
+    __syncthreads();
+
+    const int gw = warp * gridDim.x + blockIdx.x;  // consecutive tiles land on different SMs
+    const int NW = gridDim.x * kWarpsPerCta;
+    const int n_tiles = p.n_strips * p.n_chunks;
+    const int rows_own = p.own_hi - p.own_lo;
+    const int n_bnd = (p.n_chunks > 1 ? 2 : 1) * p.n_strips;
+    uint32_t it = 0;
+    unsigned long long epoch = 0;
+
+    for (int sw = 0; sw < p.sweeps; ++sw) {
+        const int par = (p.first_parity + sw) & 1;
+        const CUtensorMap* tm_in = par ? &tmB : &tmA;
+        T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
+        T* up_out = reinterpret_cast<T*>(p.up_buf[par ^ 1]);
+        T* dn_out = reinterpret_cast<T*>(p.dn_buf[par ^ 1]);
+        const unsigned long long need_up = p.flag_base_up + (unsigned long long)sw * p.n_strips;
+        const unsigned long long need_dn = p.flag_base_dn + (unsigned long long)sw * p.n_strips;
+        double* partials = p.partials + (size_t)(sw & 1) * n_tiles * 2;
+
+        for (int q = gw; q < n_tiles; q += NW) {
+            if (aborted(p)) break;
+            int chunk, strip;
+            if (q < p.n_strips) {
+                chunk = 0;
+                strip = q;
+            } else if (q < n_bnd) {
+                chunk = p.n_chunks - 1;
+                strip = q - p.n_strips;
+            } else {
+                const int r = q - n_bnd;
+                chunk = 1 + r / p.n_strips;
+                strip = r - (chunk - 1) * p.n_strips;
+            }
+            const int y0 = p.own_lo + (int)((long long)rows_own * chunk / p.n_chunks);
+            const int y1 = p.own_lo + (int)((long long)rows_own * (chunk + 1) / p.n_chunks);
+            const int x_ld = strip * OUTW - M * VEC;
+            const bool top = (chunk == 0), bot = (chunk == p.n_chunks - 1);
+
+            // Ghost rows this tile reads were written by the neighbour during its previous sweep.
+            if (lane == 0) {
+                bool ok = true;
+                if (top && p.up_buf[0] != nullptr) ok = wait_counter_sys(p, &p.my_flags[0], need_up);
+                if (ok && bot && p.dn_buf[0] != nullptr) ok = wait_counter_sys(p, &p.my_flags[1], need_dn);
+                ptx::fence_proxy_async();  // peer stores (generic proxy) -> our TMA loads (async proxy)
+                (void)ok;
+            }
+            __syncwarp();
+            if (aborted(p)) break;
+
+            const int gy_lo = p.row0 + y0 - TB, gy_hi = p.row0 + y1 + TB - 1;
+            const bool masked = (gy_lo < p.ylo) || (gy_hi > p.yhi) || (x_ld < p.xlo) ||
+                                (x_ld + 32 * VEC - 1 > p.xhi);
+            double rs = 0.0, rm = 0.0;
+            if (masked)
+                process_tile<Op, TB, true, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane,
+                                                rs, rm);
+            else
+                process_tile<Op, TB, false, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it,
+                                                 lane, rs, rm);
+
+            if (RES) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    rs += __shfl_xor_sync(0xffffffffu, rs, o);
+                    rm = fmax(rm, __shfl_xor_sync(0xffffffffu, rm, o));
+                }
+                if (lane == 0) {
+                    partials[2 * q] = rs;
+                    partials[2 * q + 1] = rm;
+                }
+            }
+            // Publish the halo rows this tile pushed: all lanes' peer stores -> one release per neighbour.
+            __syncwarp();
+            if (lane == 0) {
+                if (top && up_out != nullptr) {
+                    ptx::fence_acq_rel_sys();
+                    ptx::red_add_release_sys(p.up_flag, 1ull);
+                }
+                if (bot && dn_out != nullptr) {
+                    ptx::fence_acq_rel_sys();
+                    ptx::red_add_release_sys(p.dn_flag, 1ull);
+                }
+            }
+        }
+
+        const bool last = (sw + 1 == p.sweeps);
+        if (!last || RES) grid_barrier(p, epoch);
+        if (aborted(p)) break;
+
+        if (RES && blockIdx.x == 0) {
+            // fixed-order reduction of the per-tile partials -> one (sumsq, max) per sweep
+            double a = 0.0, b = 0.0;
+            for (int i = threadIdx.x; i < n_tiles; i += kThreads) {
+                a += __ldcg(&partials[2 * i]);
+                b = fmax(b, __ldcg(&partials[2 * i + 1]));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a += __shfl_xor_sync(0xffffffffu, a, o);
+                b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+            }
+            if (lane == 0) {
+                red_ss[warp] = a;
+                red_mx[warp] = b;
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double sa = 0.0, sb = 0.0;
+                for (int k = 0; k < kThreads / 32; ++k) {
+                    sa += red_ss[k];
+                    sb = fmax(sb, red_mx[k]);
+                }
+                const int slot = p.res_slot0 + sw;
+                if (slot < kMaxResSlots) {
+                    p.res_out[2 * slot] = sa;
+                    p.res_out[2 * slot + 1] = sb;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host plan
+
+}  // namespace mcp
+
+using namespace mcp;
+
+struct mcp_fused2d_plan {
+    mcp_fused2d_desc d;
+    int rows_alloc;
+    int sm_count;
+    int grid;
+    int parity;
+    CUtensorMap tm[2];
+    unsigned long long* grid_bar;
+    int* status;
+    double* partials;
+    size_t partials_cap_tiles;
+    double* res_out;
+    unsigned long long flag_base_up, flag_base_dn, bar_base;
+    int res_slots_used;
+    int64_t launches;
+    unsigned long long timeout_ns;
+};
+
+namespace {
+
+int vec_of(int dtype) { return dtype == MCP_DTYPE_F64 ? 2 : 4; }
+
+int outw_rt(int dtype, int tb) {
+    const int vec = vec_of(dtype);
+    return (32 - 2 * ((tb + vec - 1) / vec)) * vec;
+}
+
+int max_tb(int op, int dtype) {
+    if (op == MCP_OP_LIFE) return 4;
+    return dtype == MCP_DTYPE_F64 ? 4 : 8;
+}
+
+void choose_geometry(const mcp_fused2d_plan* pl, int tb, int* n_strips, int* n_chunks) {
+    const mcp_fused2d_desc& d = pl->d;
+    const int outw = outw_rt(d.dtype, tb);
+    const int ns = (int)ceil_div(d.w, outw);
+    const int G = d.ghost;
+    const int max_chunks = std::max(1, d.rows_own / std::max(G, 1));
+    int nc;
+    if (d.chunk_rows > 0) {
+        nc = (int)ceil_div(d.rows_own, d.chunk_rows);
+    } else {
+        // Pick the chunk count whose tile count best fills an integer number of waves over all warps
+        // while keeping the 2*TB redundant pre-roll rows per chunk small.
+        const int NW = pl->grid * kWarpsPerCta;
+        double best = -1.0;
+        nc = 1;
+        const int lo = 1, hi = std::min(max_chunks, std::max(1, d.rows_own / 16));
+        for (int c = lo; c <= hi; ++c) {
+            const double tiles = (double)ns * c;
+            const double waves = std::ceil(tiles / NW);
+            const double balance = tiles / (waves * NW);
+            const double rows = (double)d.rows_own / c;
+            const double redundancy = rows / (rows + 2.0 * tb);
+            const double score = balance * redundancy;
+            if (score > best + 1e-9) {
+                best = score;
+                nc = c;
+            }
+        }
+    }
+    nc = std::max(1, std::min(nc, max_chunks));
+    *n_strips = ns;
+    *n_chunks = nc;
+}
+
+template <class Op, int TB>
+int launch_variant(mcp_fused2d_plan* pl, const Fused2dParams& p, bool res, cudaStream_t stream) {
+    void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
+    const void* fn = res ? (const void*)fused2d_kernel<Op, TB, true> : (const void*)fused2d_kernel<Op, TB, false>;
+    MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(pl->grid), dim3(kThreads), args, kSmemBytes, stream));
+    pl->launches++;
+    return MCP_OK;
+}
+
+template <class Op>
+int launch_tb(mcp_fused2d_plan* pl, int tb, const Fused2dParams& p, bool res, cudaStream_t stream) {
+    switch (tb) {
+        case 1: return launch_variant<Op, 1>(pl, p, res, stream);
+        case 2: return launch_variant<Op, 2>(pl, p, res, stream);
+        case 4: return launch_variant<Op, 4>(pl, p, res, stream);
+        default: break;
+    }
+    set_error("unsupported time block %d", tb);
+    return MCP_ERR_UNSUPPORTED;
+}
+
+int launch_any(mcp_fused2d_plan* pl, int tb, const Fused2dParams& p, bool res, cudaStream_t stream) {
+    const mcp_fused2d_desc& d = pl->d;
+    if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F32) {
+        if (tb == 8) return launch_variant<MdfF32, 8>(pl, p, res, stream);
+        return launch_tb<MdfF32>(pl, tb, p, res, stream);
+    }
+    if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F64) return launch_tb<MdfF64>(pl, tb, p, res, stream);
+    if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_I32) return launch_tb<LifeI32>(pl, tb, p, res, stream);
+    set_error("unsupported op/dtype combination %d/%d", d.op, d.dtype);
+    return MCP_ERR_UNSUPPORTED;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out) {
+    MCP_REQUIRE(desc && plan_out, "mcp_fused2d_create: null argument");
+    const mcp_fused2d_desc& d = *desc;
+    MCP_REQUIRE(d.op == MCP_OP_MDF || d.op == MCP_OP_LIFE, "bad op %d", d.op);
+    MCP_REQUIRE((d.op == MCP_OP_LIFE) == (d.dtype == MCP_DTYPE_I32), "op %d does not take dtype %d", d.op, d.dtype);
+    MCP_REQUIRE(d.h >= 1 && d.w >= 1 && d.rows_own >= 1, "empty grid");
+    MCP_REQUIRE(d.ghost >= 1 && d.ghost <= 8, "ghost depth %d outside [1,8]", d.ghost);
+    MCP_REQUIRE(d.pitch >= d.w && d.pitch % 32 == 0, "pitch %lld must be a multiple of 32 and >= w", (long long)d.pitch);
+    MCP_REQUIRE(d.buf[0] && d.buf[1], "null field buffer");
+    MCP_REQUIRE(((uintptr_t)d.buf[0] % 128 == 0) && ((uintptr_t)d.buf[1] % 128 == 0), "buffers must be 128-byte aligned");
+    MCP_REQUIRE((d.up_buf[0] == nullptr) == (d.up_buf[1] == nullptr), "up_buf must be both set or both null");
+    MCP_REQUIRE((d.dn_buf[0] == nullptr) == (d.dn_buf[1] == nullptr), "dn_buf must be both set or both null");
+    if (d.up_buf[0] || d.dn_buf[0]) {
+        MCP_REQUIRE(d.flags != nullptr, "flags required when neighbours exist");
+        MCP_REQUIRE(d.rows_own >= d.ghost, "a slab of %d rows is thinner than the ghost depth %d", d.rows_own, d.ghost);
+    }
+    MCP_REQUIRE(!d.up_buf[0] || d.up_flag, "up_flag required with up_buf");
+    MCP_REQUIRE(!d.dn_buf[0] || d.dn_flag, "dn_flag required with dn_buf");
+
+    mcp_fused2d_plan* pl = new (std::nothrow) mcp_fused2d_plan();
+    MCP_REQUIRE(pl, "out of host memory");
+    pl->d = d;
+    pl->rows_alloc = d.rows_own + 2 * d.ghost;
+    pl->parity = 0;
+    pl->flag_base_up = pl->flag_base_dn = pl->bar_base = 0;
+    pl->res_slots_used = 0;
+    pl->launches = 0;
+    pl->timeout_ns = 20ull * 1000000000ull;
+    pl->grid_bar = nullptr;
+    pl->status = nullptr;
+    pl->partials = nullptr;
+    pl->res_out = nullptr;
+
+    int rc = device_sm_count(&pl->sm_count);
+    if (rc) { delete pl; return rc; }
+    pl->grid = pl->sm_count;
+    if (d.max_ctas > 0) pl->grid = std::min(pl->grid, d.max_ctas);
+
+    const int esz = d.dtype == MCP_DTYPE_F64 ? 8 : 4;
+    for (int b = 0; b < 2; ++b) {
+        uint64_t dims[2] = {(uint64_t)d.pitch, (uint64_t)pl->rows_alloc};
+        uint64_t strides[1] = {(uint64_t)d.pitch * esz};
+        uint32_t box[2] = {(uint32_t)(kRowBytes / esz), (uint32_t)kRowsPerStage};
+        rc = encode_tensor_map(&pl->tm[b], d.dtype, 2, d.buf[b], dims, strides, box);
+        if (rc) { delete pl; return rc; }
+    }
+    // scratch: grid barrier counter, status word, residual partials + history
+    const int min_outw = outw_rt(d.dtype, max_tb(d.op, d.dtype));
+    const size_t max_strips = (size_t)ceil_div(d.w, min_outw);
+    const size_t max_chunks = (size_t)std::max(1, d.rows_own / std::max(d.ghost, 1));
+    pl->partials_cap_tiles = max_strips * std::min<size_t>(max_chunks, 4096);
+    cudaError_t e;
+    if ((e = cudaMalloc(&pl->grid_bar, 256)) != cudaSuccess || (e = cudaMemset(pl->grid_bar, 0, 256)) != cudaSuccess ||
+        (e = cudaMalloc(&pl->status, 256)) != cudaSuccess || (e = cudaMemset(pl->status, 0, 256)) != cudaSuccess ||
+        (e = cudaMalloc(&pl->partials, pl->partials_cap_tiles * 4 * sizeof(double))) != cudaSuccess ||
+        (e = cudaMalloc(&pl->res_out, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
+        (e = cudaMemset(pl->res_out, 0, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess) {
+        set_error("mcp_fused2d_create: scratch allocation failed: %s", cudaGetErrorString(e));
+        mcp_fused2d_destroy(pl);
+        return MCP_ERR_CUDA;
+    }
+    *plan_out = pl;
+    return MCP_OK;
+}
+
+int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_strips, int* n_chunks, int* grid,
+                         int* smem_bytes) {
+    MCP_REQUIRE(pl, "null plan");
+    int ns, nc;
+    choose_geometry(pl, time_block, &ns, &nc);
+    if (n_strips) *n_strips = ns;
+    if (n_chunks) *n_chunks = nc;
+    if (grid) *grid = pl->grid;
+    if (smem_bytes) *smem_bytes = kSmemBytes;
+    return MCP_OK;
+}
+
+int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int residual_mode, void* stream_) {
+    MCP_REQUIRE(pl, "null plan");
+    MCP_REQUIRE(generations >= 0, "negative generation count");
+    const mcp_fused2d_desc& d = pl->d;
+    const int tbmax = std::min(max_tb(d.op, d.dtype), d.ghost);
+    MCP_REQUIRE(time_block >= 1, "time_block must be >= 1");
+    int tb = 1;
+    while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const bool res = residual_mode != MCP_RES_NONE;
+    if (res) pl->res_slots_used = 0;
+
+    int remaining = generations;
+    while (remaining > 0) {
+        while (tb > remaining) tb >>= 1;
+        const int sweeps = remaining / tb;
+        int ns, nc;
+        choose_geometry(pl, tb, &ns, &nc);
+        MCP_REQUIRE((size_t)ns * nc <= pl->partials_cap_tiles, "tile count %d x %d exceeds scratch capacity", ns, nc);
+
+        Fused2dParams p;
+        memset(&p, 0, sizeof(p));
+        for (int b = 0; b < 2; ++b) {
+            p.buf[b] = d.buf[b];
+            p.up_buf[b] = d.up_buf[b];
+            p.dn_buf[b] = d.dn_buf[b];
+        }
+        p.my_flags = (const unsigned long long*)d.flags;
+        p.up_flag = (unsigned long long*)d.up_flag;
+        p.dn_flag = (unsigned long long*)d.dn_flag;
+        p.grid_bar = pl->grid_bar;
+        p.status = pl->status;
+        p.partials = pl->partials;
+        p.res_out = pl->res_out;
+        p.flag_base_up = pl->flag_base_up;
+        p.flag_base_dn = pl->flag_base_dn;
+        p.bar_base = pl->bar_base;
+        p.timeout_ns = pl->timeout_ns;
+        p.pitch = d.pitch;
+        p.rows_alloc = pl->rows_alloc;
+        p.h = d.h;
+        p.w = d.w;
+        p.row0 = d.row_start - d.ghost;
+        p.own_lo = d.ghost;
+        p.own_hi = d.ghost + d.rows_own;
+        p.ylo = d.ylo; p.yhi = d.yhi; p.xlo = d.xlo; p.xhi = d.xhi;
+        p.G = d.ghost;
+        p.up_ghost_row = d.ghost + d.up_rows_own;
+        p.n_strips = ns;
+        p.n_chunks = nc;
+        p.sweeps = sweeps;
+        p.first_parity = pl->parity;
+        p.res_slot0 = pl->res_slots_used;
+
+        int rc = launch_any(pl, tb, p, res, stream);
+        if (rc) return rc;
+
+        const unsigned long long barriers = res ? (unsigned long long)sweeps : (unsigned long long)(sweeps - 1);
+        pl->bar_base += barriers * (unsigned long long)pl->grid;
+        pl->flag_base_up += (unsigned long long)sweeps * ns;
+        pl->flag_base_dn += (unsigned long long)sweeps * ns;
+        pl->parity = (pl->parity + sweeps) & 1;
+        if (res) pl->res_slots_used = std::min(kMaxResSlots, pl->res_slots_used + sweeps);
+        remaining -= sweeps * tb;
+    }
+    return MCP_OK;
+}
+
+int mcp_fused2d_parity(const mcp_fused2d_plan* pl) { return pl ? pl->parity : 0; }
+
+int mcp_fused2d_set_parity(mcp_fused2d_plan* pl, int parity) {
+    MCP_REQUIRE(pl, "null plan");
+    pl->parity = parity & 1;
+    return MCP_OK;
+}
+
+int mcp_fused2d_residuals(mcp_fused2d_plan* pl, double* out, int max_entries) {
+    MCP_REQUIRE(pl && out, "null argument");
+    const int n = std::min(pl->res_slots_used, max_entries);
+    if (n > 0) {
+        cudaError_t e = cudaMemcpy(out, pl->res_out, (size_t)n * 2 * sizeof(double), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            set_error("mcp_fused2d_residuals: %s", cudaGetErrorString(e));
+            return MCP_ERR_CUDA;
+        }
+    }
+    return n;
+}
+
+int mcp_fused2d_status(mcp_fused2d_plan* pl) {
+    MCP_REQUIRE(pl, "null plan");
+    int st = 0;
+    MCP_CUDA_TRY(cudaMemcpy(&st, pl->status, sizeof(int), cudaMemcpyDeviceToHost));
+    if (st != 0) set_error("fused2d kernel recorded status %d (%s)", st, st == MCP_ERR_TIMEOUT ? "flag/barrier wait timed out" : "error");
+    return st;
+}
+
+int64_t mcp_fused2d_launches(const mcp_fused2d_plan* pl) { return pl ? pl->launches : 0; }
+
+int mcp_fused2d_destroy(mcp_fused2d_plan* pl) {
+    if (!pl) return MCP_OK;
+    if (pl->grid_bar) cudaFree(pl->grid_bar);
+    if (pl->status) cudaFree(pl->status);
+    if (pl->partials) cudaFree(pl->partials);
+    if (pl->res_out) cudaFree(pl->res_out);
+    delete pl;
+    return MCP_OK;
+}
+
+}  // extern "C"

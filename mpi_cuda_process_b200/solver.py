@@ -1,0 +1,630 @@
+"""Solver: the generation loop, for every backend.
+
+Reference counterpart: the two copies of the ``while (iter_count > 0)`` loop in ``main()`` -- rank 0 at
+MDF_kernel.cu:155-188, "everyone else" at MDF_kernel.cu:189-222 (kernel.cu:202-269) -- which per generation
+upload the whole grid, launch middle_kernel, receive the neighbour's border row element by element, upload
+the whole grid again, launch border_kernel, synchronise, download the whole grid and send the own border
+row element by element.  As written that loop never swaps its buffers (MDF_kernel.cu:164), copies the
+input back (MDF_kernel.cu:177) and deadlocks for g >= 2 (MDF_kernel.cu:168 vs 215); the Solver implements
+the intended semantics with one code path for every rank.
+
+Backends
+  fused   persistent sm_100a kernel: TMA-fed, temporally blocked, halo rows stored into the neighbour
+          GPUs over NVLink inside the kernel, device-side flags and grid barrier (the product)
+  nccl    plain kernel per generation + grouped NCCL send/recv of ghost rows (baseline)
+  staged  the reference's host-staged pattern: D2H, host messages, H2D every generation (baseline)
+  cpu     torch CPU tensors + gloo (plumbing / correctness without a GPU)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+from dataclasses import dataclass, field
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import oracle
+from .config import RunConfig
+from .parallel.context import DistContext, init_context
+from .parallel.decomp import Decomposition
+from .parallel import host_p2p
+
+_TORCH_DTYPE = {"fp32": torch.float32, "fp64": torch.float64, "int32": torch.int32}
+_NP_DTYPE = {"fp32": np.float32, "fp64": np.float64, "int32": np.int32}
+_MCP_DTYPE = {"fp32": 0, "fp64": 1, "int32": 2}
+_MCP_OP = {"mdf": 0, "life": 1}
+
+
+@dataclass
+class RunStats:
+    generations: int = 0
+    device_ms: float = 0.0          # max over ranks, CUDA events (wall clock on the CPU backend)
+    cells: int = 0
+    launches: int = 0
+    halo_messages: int = 0
+    residual_history: List[Tuple[int, float]] = field(default_factory=list)
+
+    @property
+    def glups(self) -> float:
+        return (self.cells * self.generations) / (self.device_ms * 1e-3) / 1e9 if self.device_ms > 0 else 0.0
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class Solver:
+    """Distributed stencil solver.  Use as a context manager or call :meth:`close`."""
+
+    def __init__(self, cfg: RunConfig, ctx: Optional[DistContext] = None, device: Optional[str] = None):
+        self.cfg = cfg
+        self._own_ctx = ctx is None
+        self.ctx = ctx if ctx is not None else init_context(device="cpu" if cfg.backend == "cpu" else device)
+        self.backend = self._pick_backend()
+        self.ndim = cfg.ndim
+        self.tdtype = _TORCH_DTYPE[cfg.dtype]
+        self.npdtype = _NP_DTYPE[cfg.dtype]
+        self.esize = 8 if cfg.dtype == "fp64" else 4
+        # ghost depth: the fused kernel exchanges `time_block` rows every `time_block` generations
+        if self.backend == "fused" and self.ndim == 2:
+            tbmax = 8 if (cfg.workload == "mdf" and cfg.dtype == "fp32") else 4
+            tb = 1
+            while tb * 2 <= min(cfg.time_block, tbmax):
+                tb *= 2
+            self.time_block = tb
+            self.ghost = tb
+        else:
+            self.time_block = 1
+            self.ghost = 1
+        self.decomp = self._make_decomp()
+        self.block = self.decomp.block(self.ctx.rank)
+        self.generation = 0
+        self.total_stats = RunStats(cells=cfg.cells)
+        self._arena = None
+        self._plan = None
+        self._lib = None
+        self._closed = False
+        self._ghosts_valid = True
+        self._last_residual: Optional[Tuple[float, float]] = None
+        self._scratch = None
+        self._alloc()
+
+    # ------------------------------------------------------------------ setup
+    def _pick_backend(self) -> str:
+        b = self.cfg.backend
+        if b == "auto":
+            if not self.ctx.is_cuda:
+                return "cpu"
+            return "fused" if self.cfg.ndim == 2 else "nccl"
+        if b != "cpu" and not self.ctx.is_cuda:
+            raise RuntimeError(f"backend {b!r} needs a GPU")
+        if b == "fused" and self.cfg.ndim == 3:
+            raise ValueError("the fused backend covers the 2-D workloads; use backend='nccl' for heat3d")
+        return b
+
+    def _make_decomp(self) -> Decomposition:
+        cfg, world = self.cfg, self.ctx.world
+        if cfg.ndim == 3 and cfg.decomposition == "pencil":
+            return Decomposition.pencil(cfg.shape, world, cfg.pencil, ghost=self.ghost)
+        return Decomposition.slab(cfg.shape, world, ghost=self.ghost)
+
+    @property
+    def _fix_bounds(self):
+        """Inclusive global box of cells that evolve: (ylo, yhi, xlo, xhi)."""
+        h, w = self.cfg.height, self.cfg.width
+        if self.cfg.workload == "life" and self.cfg.bc == "dead-outside":
+            return 0, h - 1, 0, w - 1
+        return 1, h - 2, 1, w - 2
+
+    def _alloc(self) -> None:
+        cfg, G = self.cfg, self.ghost
+        own = self.block.shape
+        self.own_shape = own
+        # ghost layers on every non-contiguous axis (unused at the physical boundary: stay zero)
+        self.alloc_shape = tuple(n + 2 * G for n in own[:-1]) + (own[-1],)
+        if self.ctx.is_cuda:
+            from .ops import _lib
+            self._lib = _lib.cuda_lib()
+            self.pitch = _round_up(cfg.width, 32)
+        else:
+            self.pitch = cfg.width
+        store_shape = self.alloc_shape[:-1] + (self.pitch,)
+        self.store_shape = store_shape
+        if self.ctx.is_cuda:
+            from .parallel.arena import SymmetricArena
+            # identical layout on every rank: size buffers for the largest block
+            max_own = [max(b.shape[a] for b in self.decomp.blocks()) for a in range(self.ndim)]
+            max_alloc = 1
+            for n in max_own[:-1]:
+                max_alloc *= n + 2 * G
+            self._buf_bytes = _round_up(max_alloc * self.pitch * self.esize, 4096)
+            self._flags_bytes = 4096
+            need_peers = self.backend == "fused" and self.ctx.distributed
+            peers = [r for pair in self.block.neighbors for r in pair if r is not None] if need_peers else []
+            total = self._flags_bytes + 2 * self._buf_bytes
+            if need_peers:
+                self._arena = SymmetricArena(self.ctx, total, peers=peers)
+            else:
+                self._arena = SymmetricArena(_SoloCtx(self.ctx), total)
+            self.bufs = [self._arena.view(self._flags_bytes + i * self._buf_bytes, store_shape, self.tdtype)
+                         for i in range(2)]
+            self._scratch = torch.empty(max(1, self._lib.mcp_residual2d_scratch_bytes() // 8) + 2,
+                                        dtype=torch.float64, device=self.ctx.device)
+        else:
+            self.bufs = [torch.zeros(store_shape, dtype=self.tdtype) for _ in range(2)]
+        self.cur = 0
+
+    def _buf_ptr(self, i: int, rank: Optional[int] = None) -> int:
+        off = self._flags_bytes + i * self._buf_bytes
+        return self._arena.peer_ptr(self.ctx.rank if rank is None else rank, off)
+
+    def _stream(self) -> C.c_void_p:
+        return C.c_void_p(torch.cuda.current_stream(self.ctx.device).cuda_stream)
+
+    def _ensure_plan(self):
+        if self._plan is not None:
+            return
+        from .ops import _lib
+        cfg, G = self.cfg, self.ghost
+        d = _lib.FusedDesc()
+        d.op, d.dtype = _MCP_OP[cfg.workload], _MCP_DTYPE[cfg.dtype]
+        d.h, d.w = cfg.height, cfg.width
+        d.row_start, d.rows_own, d.ghost = self.block.start[0], self.own_shape[0], G
+        d.pitch = self.pitch
+        up, dn = self.block.neighbors[0]
+        for i in range(2):
+            d.buf[i] = self._buf_ptr(i)
+            d.up_buf[i] = self._buf_ptr(i, up) if up is not None else None
+            d.dn_buf[i] = self._buf_ptr(i, dn) if dn is not None else None
+        d.up_rows_own = self.decomp.block(up).shape[0] if up is not None else 0
+        d.flags = self._arena.peer_ptr(self.ctx.rank, 0)
+        d.up_flag = self._arena.peer_ptr(up, 8) if up is not None else None      # up's flags[1]
+        d.dn_flag = self._arena.peer_ptr(dn, 0) if dn is not None else None      # down's flags[0]
+        d.ylo, d.yhi, d.xlo, d.xhi = self._fix_bounds
+        d.chunk_rows = int(cfg.extra.get("chunk_rows", 0))
+        d.max_ctas = int(cfg.extra.get("max_ctas", 0))
+        plan = C.c_void_p()
+        _lib.check(self._lib.mcp_fused2d_create(C.byref(d), C.byref(plan)), "mcp_fused2d_create")
+        self._plan = plan
+        self._desc = d
+
+    # ------------------------------------------------------------------ initial condition
+    def initialize(self, field: Optional[np.ndarray] = None) -> None:
+        """Set generation 0.  ``field`` (global array, same on every rank) overrides the config's rule."""
+        cfg = self.cfg
+        if field is None and self.ctx.is_cuda and (cfg.workload != "life" or cfg.seed is not None):
+            self._device_init()
+        else:
+            if field is None:
+                field = self._host_init_global()
+            self.load_global(field)
+        self.generation = 0
+        self._ghosts_valid = True
+        self._reset_plan_parity()
+        self.ctx.barrier()
+
+    def _host_init_global(self) -> np.ndarray:
+        cfg = self.cfg
+        if cfg.workload == "life" and cfg.seed is None and cfg.height * cfg.width > 1 << 16:
+            from .ops import _lib
+            u = np.zeros((cfg.height, cfg.width), dtype=np.int32)
+            _lib.host_lib().mcp_host_life_init_reference(u.ctypes.data, cfg.height, cfg.width, C.c_float(cfg.prob))
+            return u
+        return oracle.init_field(cfg)
+
+    def _device_init(self) -> None:
+        from .ops import _lib
+        cfg, G = self.cfg, self.ghost
+        s = self._stream()
+        for b in self.bufs:
+            if self.ndim == 2:
+                row0 = self.block.start[0] - G
+                if cfg.workload == "life":
+                    _lib.check(self._lib.mcp_init_life_hash(b.data_ptr(), self.pitch, self.store_shape[0], row0,
+                                                            cfg.height, cfg.width, cfg.prob, cfg.seed, s))
+                else:
+                    _lib.check(self._lib.mcp_init_ring2d(_MCP_DTYPE[cfg.dtype], b.data_ptr(), self.pitch,
+                                                         self.store_shape[0], row0, cfg.height, cfg.width,
+                                                         cfg.ring, cfg.interior, s))
+            else:
+                z0, y0 = self.block.start[0] - G, self.block.start[1] - G
+                _lib.check(self._lib.mcp_init_shell3d(_MCP_DTYPE[cfg.dtype], b.data_ptr(), self.pitch,
+                                                      self.store_shape[1] * self.pitch, self.store_shape[0],
+                                                      self.store_shape[1], z0, y0, cfg.depth, cfg.height, cfg.width,
+                                                      cfg.ring, cfg.interior, s))
+        self.cur = 0
+        torch.cuda.synchronize(self.ctx.device)
+
+    def _local_from_global(self, field: np.ndarray) -> np.ndarray:
+        """This rank's allocation (owned block + ghost layers, zero outside the domain) cut from a global array."""
+        G = self.ghost
+        loc = np.zeros(self.store_shape, dtype=self.npdtype)
+        src_sl, dst_sl = [], []
+        for a in range(self.ndim - 1):
+            s, e = self.block.start[a] - G, self.block.stop[a] + G
+            cs, ce = max(s, 0), min(e, self.cfg.shape[a])
+            src_sl.append(slice(cs, ce))
+            dst_sl.append(slice(cs - s, ce - s))
+        src_sl.append(slice(0, self.cfg.width))
+        dst_sl.append(slice(0, self.cfg.width))
+        loc[tuple(dst_sl)] = field[tuple(src_sl)]
+        return loc
+
+    def load_global(self, field: np.ndarray) -> None:
+        if tuple(field.shape) != tuple(self.cfg.shape):
+            raise ValueError(f"field shape {field.shape} != configured {self.cfg.shape}")
+        loc = torch.from_numpy(self._local_from_global(np.asarray(field, dtype=self.npdtype)))
+        for b in self.bufs:
+            b.copy_(loc)
+        self.cur = 0
+        if self.ctx.is_cuda:
+            torch.cuda.synchronize(self.ctx.device)
+
+    def load_local(self, local: torch.Tensor, non_blocking: bool = True) -> None:
+        """Upload this rank's slab (owned rows + ghost rows, shape ``store_shape``) from (pinned) host memory
+        into the current buffer.  This is the public per-step input path timed by ``bench.py``'s e2e number."""
+        if tuple(local.shape) != tuple(self.store_shape):
+            raise ValueError(f"local shape {tuple(local.shape)} != {self.store_shape}")
+        if self.backend == "fused" and self.ctx.distributed:
+            # a neighbour's last halo push of the previous run may still be in flight towards our ghost rows
+            self.ctx.barrier()
+        self.bufs[self.cur].copy_(local, non_blocking=non_blocking)
+        self._ghosts_valid = True
+
+    def _reset_plan_parity(self):
+        if self._plan is not None:
+            from .ops import _lib
+            _lib.check(self._lib.mcp_fused2d_set_parity(self._plan, self.cur))
+
+    # ------------------------------------------------------------------ stepping
+    def run(self, generations: Optional[int] = None, residual: bool = False, timed: bool = True) -> RunStats:
+        """Advance ``generations`` generations (default: the configured count)."""
+        g = self.cfg.generations if generations is None else int(generations)
+        st = RunStats(generations=g, cells=self.cfg.cells)
+        if g <= 0:
+            return st
+        if self.ctx.is_cuda:
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if timed:
+                ev0.record()
+        else:
+            t0 = time.perf_counter()
+        if self.backend == "fused":
+            self._run_fused(g, residual, st)
+        elif self.backend == "nccl":
+            self._run_nccl(g, residual, st)
+        elif self.backend == "staged":
+            self._run_staged(g, residual, st)
+        else:
+            self._run_cpu(g, residual, st)
+        if self.ctx.is_cuda:
+            if timed:
+                ev1.record()
+                ev1.synchronize()
+                st.device_ms = self.ctx.all_reduce_max(ev0.elapsed_time(ev1)) if self.ctx.distributed else ev0.elapsed_time(ev1)
+        else:
+            st.device_ms = self.ctx.all_reduce_max((time.perf_counter() - t0) * 1e3)
+        self.generation += g
+        self.total_stats.generations += g
+        self.total_stats.device_ms += st.device_ms
+        self.total_stats.launches += st.launches
+        self.total_stats.halo_messages += st.halo_messages
+        return st
+
+    # -- fused ---------------------------------------------------------------------------------
+    def _run_fused(self, g: int, residual: bool, st: RunStats) -> None:
+        from .ops import _lib
+        self._ensure_plan()
+        before = self._lib.mcp_fused2d_launches(self._plan)
+        _lib.check(self._lib.mcp_fused2d_run(self._plan, g, self.time_block, 1 if residual else 0, self._stream()),
+                   "mcp_fused2d_run")
+        st.launches = int(self._lib.mcp_fused2d_launches(self._plan) - before)
+        self.cur = self._lib.mcp_fused2d_parity(self._plan)
+        if residual:
+            self._collect_fused_residual(st)
+
+    def _collect_fused_residual(self, st: RunStats) -> None:
+        buf = (C.c_double * (2 * 4096))()
+        n = self._lib.mcp_fused2d_residuals(self._plan, buf, 4096)
+        from .ops import _lib
+        _lib.check(n, "mcp_fused2d_residuals")
+        status = self._lib.mcp_fused2d_status(self._plan)
+        _lib.check(status, "fused kernel status")
+        local = [(buf[2 * i], buf[2 * i + 1]) for i in range(n)]
+        allr = self.ctx.all_gather_object(local)
+        hist = []
+        for i in range(n):
+            ss = 0.0
+            mx = 0.0
+            for r in range(self.ctx.world):     # fixed rank order -> same bits everywhere
+                ss += allr[r][i][0]
+                mx = max(mx, allr[r][i][1])
+            hist.append((ss, mx))
+        if hist:
+            self._last_residual = hist[-1]
+        kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+        st.residual_history = [(-1, (np.sqrt(ss) if kind == "l2" else mx)) for ss, mx in hist]
+
+    def check_status(self) -> None:
+        """Raise if a fused kernel recorded an error (e.g. a halo-flag wait timed out)."""
+        if self._plan is not None:
+            from .ops import _lib
+            _lib.check(self._lib.mcp_fused2d_status(self._plan), "fused kernel status")
+
+    # -- plain kernel + exchange helpers ----------------------------------------------------------
+    def _launch_plain(self, src: torch.Tensor, dst: torch.Tensor) -> None:
+        from .ops import _lib
+        cfg, G = self.cfg, self.ghost
+        s = self._stream()
+        if self.ndim == 2:
+            ylo, yhi, xlo, xhi = self._fix_bounds
+            op = _MCP_OP[cfg.workload] | (0x100 if cfg.strict_fp64_accum and cfg.dtype == "fp32" else 0)
+            _lib.check(self._lib.mcp_step2d(op, _MCP_DTYPE[cfg.dtype], src.data_ptr(), dst.data_ptr(), self.pitch,
+                                            self.store_shape[0], self.block.start[0] - G, cfg.height, cfg.width,
+                                            G, G + self.own_shape[0], ylo, yhi, xlo, xhi, s), "mcp_step2d")
+        else:
+            _lib.check(self._lib.mcp_step3d(_MCP_DTYPE[cfg.dtype], src.data_ptr(), dst.data_ptr(), self.pitch,
+                                            self.store_shape[1] * self.pitch, self.store_shape[0],
+                                            self.store_shape[1], self.block.start[0] - G, self.block.start[1] - G,
+                                            cfg.depth, cfg.height, cfg.width, G, G + self.own_shape[0], G,
+                                            G + self.own_shape[1], oracle.HEAT3D_COEFF, s), "mcp_step3d")
+
+    def _residual_plain(self, a: torch.Tensor, b: torch.Tensor) -> Tuple[float, float]:
+        """(sum of squares, max abs) of a-b over this rank's owned cells."""
+        G = self.ghost
+        if self.ctx.is_cuda and self.ndim == 2:
+            from .ops import _lib
+            out = self._scratch[-2:]
+            _lib.check(self._lib.mcp_residual2d(_MCP_DTYPE[self.cfg.dtype], a.data_ptr(), b.data_ptr(), self.pitch,
+                                                self.cfg.width, G, G + self.own_shape[0],
+                                                self._scratch.data_ptr(), out.data_ptr(), self._stream()))
+            v = out.cpu()
+            return float(v[0]), float(v[1])
+        sl = tuple(slice(G, G + n) for n in self.own_shape[:-1]) + (slice(0, self.cfg.width),)
+        d = a[sl].to(torch.float64) - b[sl].to(torch.float64)
+        return float((d * d).sum()), float(d.abs().max()) if d.numel() else 0.0
+
+    def _global_residual(self, local: Tuple[float, float]) -> Tuple[float, float]:
+        allr = self.ctx.all_gather_object(local)
+        ss = 0.0
+        mx = 0.0
+        for s_, m_ in allr:
+            ss += s_
+            mx = max(mx, m_)
+        return ss, mx
+
+    def _record_residual(self, st: RunStats, src, dst) -> None:
+        ss, mx = self._global_residual(self._residual_plain(dst, src))
+        self._last_residual = (ss, mx)
+        kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+        st.residual_history.append((self.generation + len(st.residual_history) + 1,
+                                    float(np.sqrt(ss)) if kind == "l2" else mx))
+
+    # -- nccl baseline --------------------------------------------------------------------------
+    def _run_nccl(self, g: int, residual: bool, st: RunStats) -> None:
+        from .parallel import nccl_halo
+        G = self.ghost
+        for _ in range(g):
+            src, dst = self.bufs[self.cur], self.bufs[self.cur ^ 1]
+            if not self._ghosts_valid and self.ctx.distributed:
+                for a in self.decomp.split_axes():
+                    lo, hi = self.block.neighbors[a]
+                    st.halo_messages += nccl_halo.exchange_axis(src, a, G, self.own_shape[a], lo, hi)
+            self._launch_plain(src, dst)
+            st.launches += 1
+            if residual:
+                self._record_residual(st, src, dst)
+            self.cur ^= 1
+            self._ghosts_valid = False
+
+    # -- host-staged baseline (the reference's pattern) -------------------------------------------
+    def _run_staged(self, g: int, residual: bool, st: RunStats) -> None:
+        """Per generation: kernel, full-slab D2H, host messages, full-slab H2D -- MDF_kernel.cu:161-183 with the
+        buffer swap, mirrored peers and Dirichlet mask put right."""
+        G = self.ghost
+        if not hasattr(self, "_host_stage"):
+            self._host_stage = torch.empty(self.store_shape, dtype=self.tdtype).pin_memory()
+        for _ in range(g):
+            src, dst = self.bufs[self.cur], self.bufs[self.cur ^ 1]
+            if not self._ghosts_valid and self.ctx.distributed:
+                self._host_stage.copy_(src)                       # D2H full slab (MDF_kernel.cu:177)
+                torch.cuda.synchronize(self.ctx.device)
+                for a in self.decomp.split_axes():
+                    lo, hi = self.block.neighbors[a]
+                    if a == 0 and self.ndim == 2:
+                        st.halo_messages += host_p2p.exchange_rows(self._host_stage[:, :self.cfg.width],
+                                                                   G, self.own_shape[0], lo, hi, self.ctx.cpu_group(),
+                                                                   mode=self.cfg.halo_message)
+                    else:
+                        st.halo_messages += host_p2p.exchange_axis(self._host_stage, a, G, self.own_shape[a], lo, hi,
+                                                                   self.ctx.cpu_group())
+                src.copy_(self._host_stage, non_blocking=True)    # H2D full slab (MDF_kernel.cu:161,171)
+            self._launch_plain(src, dst)
+            st.launches += 1
+            if residual:
+                self._record_residual(st, src, dst)
+            self.cur ^= 1
+            self._ghosts_valid = False
+
+    # -- cpu --------------------------------------------------------------------------------------
+    def _cpu_step(self, src: torch.Tensor, dst: torch.Tensor) -> None:
+        cfg, G = self.cfg, self.ghost
+        dst.copy_(src)
+        if self.ndim == 2:
+            ylo, yhi, xlo, xhi = self._fix_bounds
+            r0 = self.block.start[0]
+            lo = max(r0, ylo) - r0 + G
+            hi = min(self.block.stop[0] - 1, yhi) - r0 + G + 1
+            if hi <= lo or xhi < xlo:
+                return
+            if cfg.workload == "mdf":
+                C_ = src[lo:hi, xlo:xhi + 1]
+                N_, S_ = src[lo - 1:hi - 1, xlo:xhi + 1], src[lo + 1:hi + 1, xlo:xhi + 1]
+                W_, E_ = src[lo:hi, xlo - 1:xhi], src[lo:hi, xlo + 1:xhi + 2]
+                s = E_ + W_
+                s = s + N_
+                s = s + S_
+                s = s + (-4.0) * C_
+                dst[lo:hi, xlo:xhi + 1] = 0.25 * s + C_
+            else:
+                p = torch.nn.functional.pad(src, (1, 1))
+                n = torch.zeros((hi - lo, cfg.width), dtype=torch.int32)
+                for dy in (-1, 0, 1):
+                    for dx in (0, 1, 2):
+                        if dy == 0 and dx == 1:
+                            continue
+                        n += p[lo + dy:hi + dy, dx:dx + cfg.width]
+                cur = src[lo:hi, :cfg.width]
+                new = ((n == 3) | ((n == 2) & (cur != 0))).to(torch.int32)
+                dst[lo:hi, xlo:xhi + 1] = new[:, xlo:xhi + 1]
+        else:
+            z0, y0 = self.block.start[0], self.block.start[1]
+            zl = max(z0, 1) - z0 + G
+            zh = min(self.block.stop[0] - 1, cfg.depth - 2) - z0 + G + 1
+            yl = max(y0, 1) - y0 + G
+            yh = min(self.block.stop[1] - 1, cfg.height - 2) - y0 + G + 1
+            if zh <= zl or yh <= yl or cfg.width < 3:
+                return
+            xs = slice(1, cfg.width - 1)
+            C_ = src[zl:zh, yl:yh, xs]
+            s = src[zl:zh, yl:yh, 2:cfg.width] + src[zl:zh, yl:yh, 0:cfg.width - 2]
+            s = s + src[zl:zh, yl - 1:yh - 1, xs]
+            s = s + src[zl:zh, yl + 1:yh + 1, xs]
+            s = s + src[zl - 1:zh - 1, yl:yh, xs]
+            s = s + src[zl + 1:zh + 1, yl:yh, xs]
+            d = s - 6.0 * C_
+            coeff = torch.tensor(oracle.HEAT3D_COEFF, dtype=self.tdtype)
+            dst[zl:zh, yl:yh, xs] = C_ + coeff * d
+
+    def _run_cpu(self, g: int, residual: bool, st: RunStats) -> None:
+        G = self.ghost
+        for _ in range(g):
+            src, dst = self.bufs[self.cur], self.bufs[self.cur ^ 1]
+            if not self._ghosts_valid and self.ctx.distributed:
+                for a in self.decomp.split_axes():
+                    lo, hi = self.block.neighbors[a]
+                    if a == 0 and self.ndim == 2:
+                        st.halo_messages += host_p2p.exchange_rows(src, G, self.own_shape[0], lo, hi,
+                                                                   self.ctx.cpu_group(), mode=self.cfg.halo_message)
+                    else:
+                        st.halo_messages += host_p2p.exchange_axis(src, a, G, self.own_shape[a], lo, hi,
+                                                                   self.ctx.cpu_group())
+            self._cpu_step(src, dst)
+            if residual:
+                self._record_residual(st, src, dst)
+            self.cur ^= 1
+            self._ghosts_valid = False
+
+    # ------------------------------------------------------------------ convergence
+    def run_to_tolerance(self, tol: Optional[float] = None, max_generations: Optional[int] = None,
+                         check_every: Optional[int] = None) -> RunStats:
+        """Iterate until the global residual of a generation drops to ``tol`` (extension; the reference has a
+        fixed generation count only, MDF_kernel.cu:153,157,186)."""
+        tol = self.cfg.tol if tol is None else tol
+        if tol is None:
+            raise ValueError("no tolerance given")
+        max_g = max_generations or self.cfg.max_generations or self.cfg.generations or 1 << 30
+        every = check_every or self.cfg.check_every or max(self.time_block, 1) * 25
+        if self.backend == "fused":
+            every = max(self.time_block, every // self.time_block * self.time_block)
+        total = RunStats(cells=self.cfg.cells)
+        kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+        while total.generations < max_g:
+            n = min(every, max_g - total.generations)
+            if self.backend == "fused":
+                # residual of the last generation of the last time block of this batch
+                if n > self.time_block:
+                    s0 = self.run(n - self.time_block, residual=False)
+                    total.device_ms += s0.device_ms
+                    total.launches += s0.launches
+                    s1 = self.run(self.time_block, residual=True)
+                else:
+                    s1 = self.run(n, residual=True)
+            else:
+                if n > 1:
+                    s0 = self.run(n - 1, residual=False)
+                    total.device_ms += s0.device_ms
+                    total.launches += s0.launches
+                    total.halo_messages += s0.halo_messages
+                s1 = self.run(1, residual=True)
+            total.device_ms += s1.device_ms
+            total.launches += s1.launches
+            total.halo_messages += s1.halo_messages
+            total.generations += n
+            ss, mx = self._last_residual
+            r = float(np.sqrt(ss)) if kind == "l2" else mx
+            total.residual_history.append((self.generation, r))
+            if r <= tol:
+                break
+        return total
+
+    def residual(self) -> Optional[float]:
+        """Last computed global residual (according to ``cfg.residual``), or None."""
+        if self._last_residual is None:
+            return None
+        ss, mx = self._last_residual
+        return float(np.sqrt(ss)) if self.cfg.residual == "l2" else mx
+
+    # ------------------------------------------------------------------ output
+    def local_owned(self) -> torch.Tensor:
+        """View of this rank's owned cells in the current buffer (no ghosts, no pad)."""
+        G = self.ghost
+        sl = tuple(slice(G, G + n) for n in self.own_shape[:-1]) + (slice(0, self.cfg.width),)
+        return self.bufs[self.cur][sl]
+
+    def gather(self) -> Optional[np.ndarray]:
+        """Assemble the global field on rank 0 (None elsewhere).  The reference has no gather: every rank holds
+        (a stale copy of) the whole grid (MDF_kernel.cu:137-144)."""
+        loc = self.local_owned()
+        if self.ctx.is_cuda:
+            torch.cuda.synchronize(self.ctx.device)
+        arr = loc.detach().cpu().contiguous().numpy()
+        if not self.ctx.distributed:
+            return arr.copy()
+        parts = self.ctx.all_gather_object((self.block.start, arr))
+        if self.ctx.rank != 0:
+            return None
+        out = np.zeros(self.cfg.shape, dtype=self.npdtype)
+        for start, a in parts:
+            sl = tuple(slice(s, s + n) for s, n in zip(start, a.shape))
+            out[sl] = a
+        return out
+
+    # ------------------------------------------------------------------ teardown
+    def close(self) -> None:
+        if self._closed:
+            return
+        self._closed = True
+        if self.ctx.is_cuda:
+            torch.cuda.synchronize(self.ctx.device)
+        if self._plan is not None:
+            self._lib.mcp_fused2d_destroy(self._plan)
+            self._plan = None
+        self.bufs = []
+        if self._arena is not None:
+            self._arena.close()
+            self._arena = None
+        if self._own_ctx:
+            self.ctx.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
+
+
+class _SoloCtx:
+    """Arena context for allocations that are not shared with peers."""
+
+    def __init__(self, ctx):
+        self.rank, self.world, self.device, self.distributed = ctx.rank, 1, ctx.device, False
+
+    def barrier(self):
+        pass
+
+    def all_gather_object(self, o):
+        return [o]

@@ -1,0 +1,29 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA GPU (run on a B200 with `pytest -m gpu`)")
+    config.addinivalue_line("markers", "multigpu: needs >= 2 GPUs")
+
+
+def pytest_collection_modifyitems(config, items):
+    try:
+        import torch
+        have = torch.cuda.is_available()
+        ngpu = torch.cuda.device_count() if have else 0
+    except Exception:
+        have, ngpu = False, 0
+    skip_gpu = pytest.mark.skip(reason="no CUDA GPU visible")
+    skip_multi = pytest.mark.skip(reason="needs >= 2 GPUs")
+    for item in items:
+        if "gpu" in item.keywords and not have:
+            item.add_marker(skip_gpu)
+        if "multigpu" in item.keywords and ngpu < 2:
+            item.add_marker(skip_multi)
