@@ -1,0 +1,181 @@
+#!/usr/bin/env python
+"""Headline benchmark: grid-point updates per second (GLUPS) of the 2-D 5-point MDF solve.
+
+Config (BASELINE.json #2): 16384 x 16384 fp32, 1-D slab decomposition over N GPUs of one box, fixed
+1000 iterations = ``--steps 10`` steps of 100 generations.  Strong scaling: the global grid is fixed.
+
+    python bench.py --gpus 1 --steps 10 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 10 --warmup 3
+
+Rank 0 prints ONE JSON line.  ``value`` is device-timed (CUDA events around the K steps, max over ranks);
+``e2e`` repeats the measurement through the public API with a pinned-host -> device upload of the rank's slab
+and a device -> host read of the residual inside every step.
+``--impl reference`` is the reference arm (the reference cannot be built or run here).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "grid-point updates/sec (GLUPS, device-timed, max over ranks)"
+
+
+def parse_args(argv=None):
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=10)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="fused", choices=["fused", "ours", "reference", "nccl", "staged"])
+    p.add_argument("--height", type=int, default=16384)
+    p.add_argument("--width", type=int, default=16384)
+    p.add_argument("--gens-per-step", type=int, default=100)
+    p.add_argument("--time-block", type=int, default=4)
+    p.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])
+    p.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                   help="weak: --height is per GPU (BASELINE.json config 4 uses 8192 x 8192 per GPU)")
+    p.add_argument("--chunk-rows", type=int, default=0)
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--halo-message", default="row", choices=["row", "element"])
+    return p.parse_args(argv)
+
+
+def reference_arm(args) -> int:
+    """The unmodified reference cannot run here; say why in one line (details in DESIGN.md / BASELINE.md)."""
+    why = ("reference is two bare .cu programs with no build system or Python package (pip install fails: no "
+           "setup.py/pyproject), needs MPI (mpi.h/libmpi/mpirun absent, no network), and as written deadlocks for "
+           "g>=2 (MDF_kernel.cu:168 vs :215) and reads ~16 GiB out of bounds on row 0 (MDF_kernel.cu:13-20), "
+           "which would fault the GPU")
+    rank = int(os.environ.get("RANK", "0"))
+    if rank == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why, "metric": METRIC, "n_gpus": args.gpus}))
+    return 0
+
+
+def maybe_respawn(args) -> None:
+    """``python bench.py --gpus N`` without torchrun: start the N ranks ourselves."""
+    if args.gpus > 1 and "RANK" not in os.environ:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"),
+               os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+
+
+def main(argv=None) -> int:
+    args = parse_args(argv)
+    if args.impl == "reference":
+        return reference_arm(args)
+    maybe_respawn(args)
+
+    import torch
+    from mpi_cuda_process_b200 import RunConfig, Solver
+    from mpi_cuda_process_b200.parallel.context import init_context
+    from mpi_cuda_process_b200.utils.clocks import ClockSampler
+    from mpi_cuda_process_b200.utils import metrics
+
+    ctx = init_context(device="cuda")
+    if ctx.world != args.gpus and ctx.rank == 0:
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE={ctx.world}", file=sys.stderr)
+    backend = {"ours": "fused"}.get(args.impl, args.impl)
+    h = args.height * (ctx.world if args.scaling == "weak" else 1)
+    w = args.width
+    gps = args.gens_per_step
+    cfg = RunConfig(workload="mdf", height=h, width=w, dtype=args.dtype, backend=backend,
+                    time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
+                    extra={"chunk_rows": args.chunk_rows})
+    K, W = args.steps, max(args.warmup, 0)
+
+    with Solver(cfg, ctx=ctx) as s:
+        s.initialize()
+        # ---------------- device-timed headline: K steps of `gps` generations ----------------
+        for _ in range(W):
+            s.run(gps, timed=False)
+        s.check_status()
+        ctx.barrier()
+        torch.cuda.synchronize()
+        launches0 = s.total_stats.launches
+        sampler = ClockSampler(gpu_index=ctx.device.index or 0).start() if ctx.rank == 0 else None
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(K):
+            s.run(gps, timed=False)
+        ev1.record()
+        torch.cuda.synchronize()
+        ctx.barrier()
+        clocks = sampler.stop() if sampler is not None else None
+        ms_total = ctx.all_reduce_max(ev0.elapsed_time(ev1))
+        launches = s.total_stats.launches - launches0
+        s.check_status()
+        cells = cfg.cells
+        value = cells * gps * K / (ms_total * 1e-3) / 1e9
+        geom = None
+        if backend == "fused":
+            import ctypes as C
+            ns, nc, grid, smem = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+            s._lib.mcp_fused2d_geometry(s._plan, s.time_block, C.byref(ns), C.byref(nc), C.byref(grid), C.byref(smem))
+            geom = {"strips": ns.value, "chunks": nc.value, "ctas": grid.value, "smem_bytes": smem.value}
+
+        # ---------------- end to end through the public API ----------------
+        e2e = None
+        if not args.no_e2e:
+            host = torch.empty(s.store_shape, dtype=s.tdtype).pin_memory()
+            host.copy_(s.bufs[s.cur])                     # a valid slab (incl. ghost rows) to upload every step
+            torch.cuda.synchronize()
+            h2d = host.numel() * host.element_size()
+            d2h = 16
+            def one_step():
+                s.load_local(host, non_blocking=True)     # pinned host -> device, this step's input
+                st = s.run(gps, residual=True, timed=False)   # fused residual; history read back (device -> host)
+                return st.residual_history[-1][1] if st.residual_history else s.residual()
+            for _ in range(min(W, 2)):
+                one_step()
+            torch.cuda.synchronize()
+            ctx.barrier()
+            t0 = time.perf_counter()
+            last = None
+            for _ in range(K):
+                last = one_step()
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            e2e_ms = ctx.all_reduce_max((t1 - t0) * 1e3)
+            e2e = {"value": round(cells * gps * K / (e2e_ms * 1e-3) / 1e9, 3), "unit": "GLUPS",
+                   "ms_per_step": round(e2e_ms / K, 4), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "last_residual": last}
+
+        if ctx.rank == 0:
+            esize = 8 if args.dtype == "fp64" else 4
+            cells_gpu = cells // ctx.world
+            halo = 0 if ctx.world == 1 else 2 * w * esize
+            roof = metrics.roofline(cells_gpu, gps * K, ms_total, 2 * esize, halo)
+            out = {
+                "metric": METRIC, "value": round(value, 3), "unit": "GLUPS", "n_gpus": ctx.world, "steps": K,
+                "warmup": W, "ms_per_step": round(ms_total / K, 4), "higher_is_better": True,
+                "scaling": args.scaling, "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+                "impl": args.impl if args.impl != "ours" else "fused",
+                "config": {"model": "2-D 5-point MDF (heat/Jacobi), Dirichlet ring=100", "grid": [h, w],
+                           "global_batch": cells, "seq_len": gps, "generations_per_step": gps,
+                           "iterations": gps * K, "parallelism": f"slab{ctx.world}",
+                           "time_block": s.time_block, "backend": s.backend,
+                           "l2": "inputs larger than L2 (two %d MiB buffers per GPU stream through HBM every pass)"
+                                 % (cells_gpu * esize >> 20), "geometry": geom},
+                "gpu_launches": int(launches),
+                "clocks": clocks,
+                "roofline": {k: (round(v, 4) if isinstance(v, float) else v) for k, v in roof.items()},
+            }
+            if e2e is not None:
+                out["e2e"] = e2e
+            print(json.dumps(out), flush=True)
+    ctx.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

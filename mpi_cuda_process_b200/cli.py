@@ -98,7 +98,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     cfg = RunConfig(
         workload=args.workload, generations=g, height=h, width=w, depth=args.depth,
         dtype="int32" if args.workload == "life" else args.dtype,
-        bc=args.bc or ("dead-outside" if args.workload == "life" else "fixed-ring"),
+        bc=args.bc,
         ring=args.ring, interior=args.interior, prob=args.prob, seed=args.seed, backend=args.backend,
         decomposition=args.decomposition, pencil=tuple(args.pencil), time_block=args.time_block, tol=args.tol,
         max_generations=args.max_generations, residual=args.residual, halo_message=args.halo_message,

@@ -55,7 +55,7 @@ class RunConfig:
     width: int = 256
     depth: int = 0
     dtype: str = "fp32"
-    bc: str = "fixed-ring"
+    bc: Optional[str] = None             # None = workload default (life: dead-outside, others: fixed-ring)
     ring: float = 100.0
     interior: float = 0.0
     prob: float = 0.15
@@ -86,6 +86,8 @@ class RunConfig:
             raise ValueError(f"backend must be one of {BACKENDS}, got {self.backend!r}")
         if self.dtype not in DTYPES:
             raise ValueError(f"dtype must be one of {DTYPES}, got {self.dtype!r}")
+        if self.bc is None:
+            self.bc = "dead-outside" if self.workload == "life" else "fixed-ring"
         if self.bc not in BC_MODES:
             raise ValueError(f"bc must be one of {BC_MODES}, got {self.bc!r}")
         if self.workload == "life":

@@ -34,17 +34,30 @@ def mdf_update_cells(C, N, S, W, E):
     """The pinned rounding sequence of MDF_kernel.cu:20 for arrays of one float dtype.
 
     Reference SASS: FADD(E,W); FADD(+N); FADD(+S); FFMA(C,-4,sum); then an fp64
-    DFMA(sum, 0.25, C) rounded back to fp32.  ``-4*C`` and ``0.25*s`` are exact in binary
-    floating point (power-of-two scalings), so each fused multiply-add equals the plain
-    add of the exact product and the pure-dtype expression below is bit-identical to the
-    fused forms (outside the subnormal range; tests/test_oracle.py checks the fp64 form).
+    DFMA(sum, 0.25, C) rounded back to fp32.  The GPU kernels use true fused multiply-adds:
+    ``s = fma(C, -4, s); out = fma(s, 0.25, C)``.
+
+    ``-4*C`` is exact (power-of-two scaling up), so the first fma equals a plain add of the
+    exact product.  ``0.25*s`` is exact too *except when it lands in the subnormal range*,
+    where the product loses bits while a real fma does not -- and the diffusion front of a
+    cold field does pass through subnormal values.  So the last step is evaluated the way
+    the reference does it: in fp64 (exact product, exact-enough sum: two 24-bit mantissas
+    cannot produce a double-rounding tie) and rounded once to fp32.  For fp64 fields the
+    plain expression is used, patched with extended precision where 0.25*s is subnormal.
     """
     dt = C.dtype.type
     s = E + W
     s = s + N
     s = s + S
     s = s + dt(-4.0) * C
-    return dt(0.25) * s + C
+    if C.dtype == np.float32:
+        return (s.astype(np.float64) * 0.25 + C.astype(np.float64)).astype(np.float32)
+    out = dt(0.25) * s + C
+    tiny = np.abs(s) < np.finfo(C.dtype).tiny * 8
+    if np.any(tiny & (s != 0)):
+        ls, lc = s[tiny].astype(np.longdouble), C[tiny].astype(np.longdouble)
+        out[tiny] = (ls * np.longdouble(0.25) + lc).astype(C.dtype)
+    return out
 
 
 def mdf_step(u: np.ndarray) -> np.ndarray:

@@ -467,7 +467,11 @@ class Solver:
                 s = s + N_
                 s = s + S_
                 s = s + (-4.0) * C_
-                dst[lo:hi, xlo:xhi + 1] = 0.25 * s + C_
+                if self.tdtype == torch.float32:
+                    # true fma(s, 0.25, C): exact in fp64, one rounding (0.25*s is inexact for subnormal s)
+                    dst[lo:hi, xlo:xhi + 1] = (s.double() * 0.25 + C_.double()).float()
+                else:
+                    dst[lo:hi, xlo:xhi + 1] = 0.25 * s + C_
             else:
                 p = torch.nn.functional.pad(src, (1, 1))
                 n = torch.zeros((hi - lo, cfg.width), dtype=torch.int32)

@@ -1,0 +1,89 @@
+"""Multi-GPU worker (launched by torchrun from test_gpu_multi.py or by hand under gpurun --gpus N).
+
+Runs a list of cases on all ranks, compares rank 0's gathered field with the single-domain oracle bit for
+bit, prints one JSON line per case and exits non-zero on the first mismatch."""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from mpi_cuda_process_b200 import oracle  # noqa: E402
+from mpi_cuda_process_b200.config import RunConfig  # noqa: E402
+from mpi_cuda_process_b200.parallel.context import init_context  # noqa: E402
+from mpi_cuda_process_b200.solver import Solver  # noqa: E402
+
+CASES = [
+    dict(workload="mdf", height=256, width=256, backend="fused", time_block=4, g=100),
+    dict(workload="mdf", height=263, width=389, backend="fused", time_block=1, g=7),
+    dict(workload="mdf", height=263, width=389, backend="fused", time_block=2, g=11),
+    dict(workload="mdf", height=1037, width=2050, backend="fused", time_block=4, g=203),
+    dict(workload="mdf", height=640, width=512, backend="fused", time_block=8, g=64),
+    dict(workload="mdf", height=300, width=260, backend="fused", time_block=4, g=37, dtype="fp64"),
+    dict(workload="life", height=300, width=260, backend="fused", time_block=4, g=50),
+    dict(workload="life", height=300, width=260, backend="fused", time_block=2, g=21, bc="fixed-ring"),
+    dict(workload="mdf", height=263, width=389, backend="nccl", g=9),
+    dict(workload="mdf", height=64, width=48, backend="staged", g=5),
+    dict(workload="mdf", height=40, width=24, backend="staged", g=3, halo_message="element"),
+    dict(workload="life", height=120, width=100, backend="nccl", g=15),
+    dict(workload="heat3d", depth=40, height=36, width=70, backend="nccl", g=6),
+    dict(workload="heat3d", depth=40, height=36, width=70, backend="nccl", g=6, decomposition="pencil"),
+]
+
+
+def main() -> int:
+    ctx = init_context()
+    rc = 0
+    for case in CASES:
+        case = dict(case)
+        g = case.pop("g")
+        if case.get("decomposition") == "pencil" and ctx.world < 4:
+            continue
+        cfg = RunConfig(**case)
+        with Solver(cfg, ctx=ctx) as s:
+            s.initialize()
+            st = s.run(g, residual=False)
+            s.check_status()
+            got = s.gather()
+            backend = s.backend
+        if ctx.rank == 0:
+            ref = oracle.run_field(cfg, oracle.init_field(cfg), g)
+            ok = got.tobytes() == ref.tobytes()
+            print(json.dumps({"case": case, "g": g, "world": ctx.world, "backend": backend, "bitwise": ok,
+                              "ms": round(st.device_ms, 3)}), flush=True)
+            if not ok:
+                bad = np.argwhere(got != ref)
+                print("first mismatches:", bad[:5].tolist(), file=sys.stderr, flush=True)
+                rc = 1
+        rc = ctx.broadcast_object(rc, 0)
+        if rc:
+            break
+    # fused residual across ranks: identical on all ranks and equal to the oracle's max
+    if rc == 0:
+        cfg = RunConfig(workload="mdf", height=200, width=300, backend="fused", time_block=4, residual="linf")
+        with Solver(cfg, ctx=ctx) as s:
+            s.initialize()
+            st = s.run(8, residual=True)
+            u = oracle.mdf_init(200, 300)
+            exp = []
+            for gen in range(1, 9):
+                v = oracle.mdf_step(u)
+                if gen % 4 == 0:
+                    exp.append(oracle.residual(v, u, "linf"))
+                u = v
+            got = [r for _, r in st.residual_history]
+            allg = ctx.all_gather_object(got)
+            ok = all(a == exp for a in allg)
+            if ctx.rank == 0:
+                print(json.dumps({"case": "fused residual", "world": ctx.world, "equal_on_all_ranks": ok}), flush=True)
+            if not ok:
+                rc = 1
+    ctx.close()
+    return rc
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -115,3 +115,18 @@ def test_hash_init_density():
     u = oracle.life_init_hash(200, 200, 0.15, seed=7)
     d = u[1:-1, 1:-1].mean()
     assert 0.12 < d < 0.18 and (u[0] == 0).all()
+
+
+def test_mdf_subnormal_front_matches_true_fma():
+    """The diffusion front passes through subnormal values, where 0.25*s is not exact: the oracle must
+    behave like a real fused multiply-add (what the GPU and the reference's DFMA do)."""
+    lib = _lib.host_lib()
+    u = oracle.mdf_init(200, 200)
+    v = u.copy()
+    out = np.empty_like(u)
+    for _ in range(80):
+        lib.mcp_host_mdf_step_f32(v.ctypes.data, out.ctypes.data, 200, 200, 0)
+        v, out = out, v
+        u = oracle.mdf_step(u)
+    assert np.any((np.abs(u) > 0) & (np.abs(u) < np.finfo(np.float32).tiny))   # subnormals are present
+    assert u.tobytes() == v.tobytes()
