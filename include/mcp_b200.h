@@ -121,6 +121,25 @@ size_t mcp_residual2d_scratch_bytes(void);
 int mcp_residual2d(int dtype, const void* a_dev, const void* b_dev, int64_t pitch, int w, int row_lo, int row_hi,
                    void* scratch_dev, double* out_dev, void* stream);
 
+/* Same result as mcp_residual2d, for callers that cannot allocate device memory at all (a host whose GPU memory
+ * is entirely owned by another allocator, a fixed-budget service, a plug-in forbidden to allocate after
+ * start-up, a loop that cannot tolerate the synchronisation cudaMalloc may imply): the scratch is a fixed array
+ * built into the library image, so the caller passes only inputs and the 2-double output.
+ * Limits and rules:
+ *   - at most MCP_NOALLOC_MAX_ROWS rows (row_hi - row_lo) per call; more is refused with MCP_ERR_ARG and a
+ *     message -- split the range or use mcp_residual2d;
+ *   - the array (1 MiB) is held by every GPU that loads the library, until the process exits;
+ *   - one array per GPU is shared by all calls and keeps the previous call's contents (nothing needs zeroing:
+ *     each call rewrites every entry it reads); calls that overlap on one GPU race -- serialise them;
+ *   - the first call on each device looks up the array's device address (with that device current); make
+ *     that first call outside any stream capture.
+ * Makes no cudaMalloc/cudaFree call and uses no allocating library routine.
+ * No counterpart in the reference (which has no residual and no allocation-free path). */
+#define MCP_NOALLOC_MAX_ROWS 65536
+int mcp_residual2d_noalloc_max_rows(void);
+int mcp_residual2d_noalloc(int dtype, const void* a_dev, const void* b_dev, int64_t pitch, int w, int row_lo,
+                           int row_hi, double* out_dev, void* stream);
+
 /* ---- gather + pack (reference: print_array, K:115-129; no gather exists in the reference) -------- */
 /* Cast/pack owned rows [row_lo,row_hi) x [0,w) of a pitched buffer into a dense destination (which may be a
  * peer pointer on rank 0): mode 0 = raw copy, 1 = fp64 -> fp32, 2 = int32 cells -> print_array bytes

@@ -82,6 +82,8 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_destroy.argtypes = [vp]
     lib.mcp_residual2d_scratch_bytes.restype = C.c_size_t
     lib.mcp_residual2d.argtypes = [i, vp, vp, i64, i, i, i, vp, vp, vp]
+    lib.mcp_residual2d_noalloc_max_rows.restype = i
+    lib.mcp_residual2d_noalloc.argtypes = [i, vp, vp, i64, i, i, i, vp, vp]
     lib.mcp_pack_rows.argtypes = [i, i, vp, i64, i, i, i, vp, i64, vp]
 
 

@@ -29,6 +29,7 @@ CUDA_SOURCES = [
     "stencil_plain.cu",
     "stencil2d_fused.cu",
     "residual.cu",
+    "residual_noalloc.cu",
     "gather_pack.cu",
     "host_ref.cpp",
 ]
