@@ -38,7 +38,7 @@ def parse_args(argv=None):
     p.add_argument("--height", type=int, default=16384)
     p.add_argument("--width", type=int, default=16384)
     p.add_argument("--gens-per-step", type=int, default=100)
-    p.add_argument("--time-block", type=int, default=4)
+    p.add_argument("--time-block", type=int, default=8)
     p.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])
     p.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                    help="weak: --height is per GPU (BASELINE.json config 4 uses 8192 x 8192 per GPU)")
@@ -78,7 +78,7 @@ def main(argv=None) -> int:
     import torch
     from mpi_cuda_process_b200 import RunConfig, Solver
     from mpi_cuda_process_b200.parallel.context import init_context
-    from mpi_cuda_process_b200.utils.clocks import ClockSampler
+    from mpi_cuda_process_b200.utils.clocks import make_sampler
     from mpi_cuda_process_b200.utils import metrics
 
     ctx = init_context(device="cuda")
@@ -102,7 +102,7 @@ def main(argv=None) -> int:
         ctx.barrier()
         torch.cuda.synchronize()
         launches0 = s.total_stats.launches
-        sampler = ClockSampler(gpu_index=ctx.device.index or 0).start() if ctx.rank == 0 else None
+        sampler = make_sampler(ctx.device.index or 0).start() if ctx.rank == 0 else None
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         for _ in range(K):
@@ -121,7 +121,11 @@ def main(argv=None) -> int:
             import ctypes as C
             ns, nc, grid, smem = C.c_int(), C.c_int(), C.c_int(), C.c_int()
             s._lib.mcp_fused2d_geometry(s._plan, s.time_block, C.byref(ns), C.byref(nc), C.byref(grid), C.byref(smem))
-            geom = {"strips": ns.value, "chunks": nc.value, "ctas": grid.value, "smem_bytes": smem.value}
+            rows_buf = (C.c_int * 4096)()
+            nchunk = s._lib.mcp_fused2d_chunks(s._plan, s.time_block, rows_buf, 4096)
+            crow = [rows_buf[i] for i in range(max(nchunk, 0))]
+            geom = {"strips": ns.value, "chunks": nc.value, "ctas": grid.value, "smem_bytes": smem.value,
+                    "chunk_rows_first_max_last": [crow[0], max(crow), crow[-1]] if crow else None}
 
         # ---------------- end to end through the public API ----------------
         e2e = None

@@ -112,6 +112,8 @@ int mcp_fused2d_status(mcp_fused2d_plan* plan);
 int64_t mcp_fused2d_launches(const mcp_fused2d_plan* plan);
 int mcp_fused2d_geometry(const mcp_fused2d_plan* plan, int time_block, int* n_strips, int* n_chunks, int* grid,
                          int* smem_bytes);
+/* Heights of the row chunks of the tile schedule for `time_block` (queue order = chunk order). Returns the count. */
+int mcp_fused2d_chunks(const mcp_fused2d_plan* plan, int time_block, int* rows_out, int max_entries);
 int mcp_fused2d_destroy(mcp_fused2d_plan* plan);
 
 /* ---- residual of two fields (unfused; two-pass, fixed order, deterministic) ------------------------

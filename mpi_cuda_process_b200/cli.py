@@ -53,7 +53,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--backend", choices=["auto", "fused", "nccl", "staged", "cpu"], default="auto")
     p.add_argument("--decomposition", choices=["slab", "pencil"], default="slab")
     p.add_argument("--pencil", type=int, nargs=2, default=(0, 0), metavar=("PZ", "PY"))
-    p.add_argument("--time-block", type=int, default=4)
+    p.add_argument("--time-block", type=int, default=8)
     p.add_argument("--tol", type=float, default=None, help="run to tolerance on the global residual")
     p.add_argument("--max-generations", type=int, default=0)
     p.add_argument("--residual", choices=["none", "l2", "linf"], default="none")

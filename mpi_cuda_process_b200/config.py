@@ -63,7 +63,7 @@ class RunConfig:
     backend: str = "auto"
     decomposition: str = "slab"          # "slab" (1-D rows) or "pencil" (2-D over a 3-D grid)
     pencil: Tuple[int, int] = (0, 0)     # (Py, Pz) for pencil; 0 = choose
-    time_block: int = 4
+    time_block: int = 8
     tol: Optional[float] = None
     max_generations: int = 0
     residual: str = "none"

@@ -79,6 +79,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_launches.argtypes = [vp]
     lib.mcp_fused2d_launches.restype = i64
     lib.mcp_fused2d_geometry.argtypes = [vp, i, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i)]
+    lib.mcp_fused2d_chunks.argtypes = [vp, i, vp, i]
     lib.mcp_fused2d_destroy.argtypes = [vp]
     lib.mcp_residual2d_scratch_bytes.restype = C.c_size_t
     lib.mcp_residual2d.argtypes = [i, vp, vp, i64, i, i, i, vp, vp, vp]

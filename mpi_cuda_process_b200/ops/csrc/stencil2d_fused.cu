@@ -26,6 +26,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <cmath>
 #include <new>
 #include <vector>
 
@@ -42,7 +43,11 @@ constexpr int kRowsPerStage = 6;  // multiple of 3: the 3-row register window ro
 constexpr int kStages = 4;
 constexpr int kRowBytes = 512;  // 32 lanes x 16 B
 constexpr int kStageBytes = kRowsPerStage * kRowBytes;
-constexpr int kSmemBytes = kWarpsPerCta * kStages * kStageBytes + kWarpsPerCta * kStages * 8;
+constexpr int smem_bytes_for(int warps) { return warps * kStages * kStageBytes + warps * kStages * 8; }
+constexpr int kSmemBytes = smem_bytes_for(kWarpsPerCta);
+// TB = 8 keeps 96 registers of row windows per thread: run 12 warps x 168 registers instead of 16 x 128.
+constexpr int kWarpsTb8 = 8;
+__host__ __device__ constexpr int warps_for_tb(int tb) { return tb >= 8 ? kWarpsTb8 : kWarpsPerCta; }
 constexpr int kMaxResSlots = 4096;
 
 struct Fused2dParams {
@@ -53,11 +58,14 @@ struct Fused2dParams {
     unsigned long long* up_flag;
     unsigned long long* dn_flag;
     unsigned long long* grid_bar;
+    unsigned long long* tile_ctr;
     int* status;
     double* partials;  // [2][n_tiles][2]
     double* res_out;   // [kMaxResSlots][2]
+    const int* chunk_y;  // [n_chunks + 1] local row boundaries of the row chunks (host-built schedule)
     unsigned long long flag_base_up, flag_base_dn;
     unsigned long long bar_base;
+    unsigned long long ctr_base;
     unsigned long long timeout_ns;
     long long pitch;
     int rows_alloc, h, w, row0;
@@ -244,12 +252,73 @@ __device__ __noinline__ void grid_barrier(const Fused2dParams& p, unsigned long 
 
 // ------------------------------------------------------------------------------------------ tile
 
-template <class Op, int TB, bool MASKED, bool RES>
+// 16-byte store with a predicate instead of a branch (keeps the row loop free of control flow).
+__device__ __forceinline__ void st_global_v4_pred(void* p, const uint4& v, bool pred) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+        "@q st.global.v4.u32 [%0], {%1, %2, %3, %4};\n\t}"
+        ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"((int)pred)
+        : "memory");
+}
+__device__ __forceinline__ uint4 ld_global_v4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+
+// One shared-memory stage = kRowsPerStage input rows pushed through the TB-level register wavefront.
+// GENERAL: cells may be fixed (boundary masks) and some output rows may fall outside [y0, y1).
+// !GENERAL: the lean path used by almost every iteration -- no masks, no range checks, no branches.
+template <class Op, int TB, bool GENERAL, bool RES>
+__device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const uint8_t* sp,
+                                           typename Op::T*& optr, const long long pitch, const int cbase,
+                                           const int n_in, const int gy_base, const int ylo, const int yhi,
+                                           const unsigned colfix, const bool lane_valid, const bool lane_store,
+                                           double& rs, double& rm) {
+    using V = typename Op::V;
+#pragma unroll
+    for (int j = 0; j < kRowsPerStage; ++j) {
+        L[0][mod3(j)] = Op::make_row(bitcast_v<V>(ptx::ld_shared_v4(sp + j * kRowBytes)));
+#pragma unroll
+        for (int t = 1; t <= TB; ++t) {
+            const int sc = mod3(j - t), sn = mod3(j - t - 1), ss = mod3(j - t + 1);
+            // Pre-roll: level t's first meaningful row appears at input counter 2t; anything earlier would be
+            // computed from rows that do not exist and is never read by a meaningful cell -- skip it.
+            if (GENERAL && (cbase + j < 2 * t)) continue;
+            V res = Op::update(L[t - 1][sn], L[t - 1][sc], L[t - 1][ss]);
+            if (GENERAL) {
+                const int gy = gy_base + j - t;
+                const unsigned m = (gy < ylo || gy > yhi) ? 0xfu : colfix;
+                res = Op::select(m, L[t - 1][sc].v, res);
+            }
+            if (t < TB) {
+                L[t < TB ? t : 0][sc] = Op::make_row(res);
+            } else {
+                bool row_ok = true;
+                if (GENERAL) {
+                    const int c = cbase + j;
+                    row_ok = (c >= 2 * TB) && (c < n_in);
+                }
+                if (RES) {
+                    if (row_ok && lane_valid) Op::accum(res, L[TB - 1][sc].v, rs, rm);
+                }
+                st_global_v4_pred(optr, bitcast_u<V>(res), lane_store && row_ok);
+            }
+        }
+        optr += pitch;  // one output row per input row, whether or not it was stored
+    }
+}
+
+template <class Op, int TB, bool RES>
 __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUtensorMap* tm_in,
                                              typename Op::T* __restrict__ out, typename Op::T* up_out,
                                              typename Op::T* dn_out, const int x_ld, const int y0, const int y1,
                                              uint8_t* my_smem, uint64_t* bars, uint32_t& it, const int lane,
                                              double& rs, double& rm) {
+    using T = typename Op::T;
     using V = typename Op::V;
     using Row = typename Op::Row;
     constexpr int VEC = Op::VEC;
@@ -261,17 +330,14 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
     const int cx = x_ld + lane * VEC;
 
     unsigned colfix = 0;
-    if (MASKED) {
 #pragma unroll
-        for (int v = 0; v < VEC; ++v) {
-            const int gx = cx + v;
-            if (gx < p.xlo || gx > p.xhi) colfix |= 1u << v;
-        }
+    for (int v = 0; v < VEC; ++v) {
+        const int gx = cx + v;
+        if (gx < p.xlo || gx > p.xhi) colfix |= 1u << v;
     }
+    const bool col_masked = (x_ld < p.xlo) || (x_ld + 32 * VEC - 1 > p.xhi);
     const bool lane_valid = (lane >= M) && (lane < 32 - M);
     const bool lane_store = lane_valid && (cx < (int)p.pitch);
-    const bool push_up = (up_out != nullptr) && (y0 < p.own_lo + p.G);
-    const bool push_dn = (dn_out != nullptr) && (y1 > p.own_hi - p.G);
 
     Row L[TB][3];
 #pragma unroll
@@ -290,54 +356,83 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
         for (int i = 0; i < npro; ++i) issue(it + i, ys + i * kRowsPerStage);
     }
 
+    // output pointer of the row produced by input-row counter c: local row ys + c - TB
+    T* optr = out + (long long)(ys - TB) * p.pitch + cx;
+
     for (int i = 0; i < n_it; ++i) {
         const uint32_t st = it % kStages, par = (it / kStages) & 1u;
         ptx::mbar_wait(&bars[st], par);
         const uint8_t* sp = my_smem + st * kStageBytes + lane * 16;
         const int cbase = i * kRowsPerStage;
-#pragma unroll
-        for (int j = 0; j < kRowsPerStage; ++j) {
-            const int c = cbase + j;  // input-row counter within the tile; local row = ys + c
-            L[0][mod3(j)] = Op::make_row(bitcast_v<V>(ptx::ld_shared_v4(sp + j * kRowBytes)));
-#pragma unroll
-            for (int t = 1; t <= TB; ++t) {
-                const int sc = mod3(j - t), sn = mod3(j - t - 1), ss = mod3(j - t + 1);
-                V res = Op::update(L[t - 1][sn], L[t - 1][sc], L[t - 1][ss]);
-                if (MASKED) {
-                    const int gy = p.row0 + ys + c - t;
-                    const unsigned m = (gy < p.ylo || gy > p.yhi) ? 0xfu : colfix;
-                    res = Op::select(m, L[t - 1][sc].v, res);
-                }
-                if (t < TB) {
-                    L[t < TB ? t : 0][sc] = Op::make_row(res);
-                } else {
-                    const int r_out = ys + c - TB;
-                    if (r_out >= y0 && r_out < y1) {
-                        if (RES) {
-                            if (lane_valid) Op::accum(res, L[TB - 1][sc].v, rs, rm);
-                        }
-                        if (lane_store) {
-                            const uint4 bits = bitcast_u<V>(res);
-                            ptx::st_global_v4(out + (long long)r_out * p.pitch + cx, bits);
-                            if (push_up && r_out < p.own_lo + p.G)
-                                ptx::st_global_v4(
-                                    up_out + (long long)(p.up_ghost_row + (r_out - p.own_lo)) * p.pitch + cx, bits);
-                            if (push_dn && r_out >= p.own_hi - p.G)
-                                ptx::st_global_v4(dn_out + (long long)(r_out - (p.own_hi - p.G)) * p.pitch + cx,
-                                                  bits);
-                        }
-                    }
-                }
-            }
-        }
+        const int gy_base = p.row0 + ys + cbase;  // global row of this stage's first input row
+        const bool general = col_masked || (gy_base - TB < p.ylo) || (gy_base + kRowsPerStage > p.yhi) ||
+                             (cbase < 2 * TB) || (cbase + kRowsPerStage > n_in);
+        if (general)
+            stage_rows<Op, TB, true, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix, lane_valid,
+                                          lane_store, rs, rm);
+        else
+            stage_rows<Op, TB, false, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix,
+                                           lane_valid, lane_store, rs, rm);
         __syncwarp();
         if (lane == 0 && i + kStages < n_it) issue(it + kStages, ys + (i + kStages) * kRowsPerStage);
         ++it;
     }
+
+    // Halo push: re-read the boundary rows this lane just stored (same thread, same addresses) and store them
+    // into the neighbour GPU's ghost rows over NVLink.  Kept out of the row loop so interior tiles pay nothing.
+    if (lane_store) {
+        if (up_out != nullptr) {
+            const int r1 = min(y1, p.own_lo + p.G);
+            for (int r = y0; r < r1; ++r) {
+                const uint4 v = ld_global_v4(out + (long long)r * p.pitch + cx);
+                ptx::st_global_v4(up_out + (long long)(p.up_ghost_row + (r - p.own_lo)) * p.pitch + cx, v);
+            }
+        }
+        if (dn_out != nullptr) {
+            const int r0 = max(y0, p.own_hi - p.G);
+            for (int r = r0; r < y1; ++r) {
+                const uint4 v = ld_global_v4(out + (long long)r * p.pitch + cx);
+                ptx::st_global_v4(dn_out + (long long)(r - (p.own_hi - p.G)) * p.pitch + cx, v);
+            }
+        }
+    }
 }
 
-template <class Op, int TB, bool RES>
-__global__ void __launch_bounds__(kThreads, 1)
+// Tile order: slab-cut chunks first (their halo pushes overlap everything else), then the remaining tiles of
+// the two edge strips (fully masked = slowest, so they must not end up in the tail), then the interior.
+__device__ __forceinline__ void decode_tile(int q, int ns, int nc, int& chunk, int& strip) {
+    if (q < ns) {
+        chunk = 0;
+        strip = q;
+        return;
+    }
+    q -= ns;
+    if (nc == 1) {  // unreachable for q < n_tiles
+        chunk = 0;
+        strip = 0;
+        return;
+    }
+    if (q < ns) {
+        chunk = nc - 1;
+        strip = q;
+        return;
+    }
+    q -= ns;
+    const int mid = nc - 2;  // interior chunks 1 .. nc-2
+    const int n_edge = ns >= 2 ? 2 : 1;
+    if (q < n_edge * mid) {
+        chunk = 1 + q / n_edge;
+        strip = (q % n_edge) ? ns - 1 : 0;
+        return;
+    }
+    q -= n_edge * mid;
+    const int inner = ns - 2;  // interior strips 1 .. ns-2 (>= 1 here)
+    chunk = 1 + q / inner;
+    strip = 1 + q % inner;
+}
+
+template <class Op, int TB, bool RES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
 fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ Fused2dParams p) {
     using T = typename Op::T;
@@ -348,8 +443,8 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t* my_smem = smem + warp * (kStages * kStageBytes);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWarpsPerCta * kStages * kStageBytes) + warp * kStages;
-    __shared__ double red_ss[kThreads / 32], red_mx[kThreads / 32];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WARPS * kStages * kStageBytes) + warp * kStages;
+    __shared__ double red_ss[WARPS], red_mx[WARPS];
 
     if (lane == 0) {
         for (int s = 0; s < kStages; ++s) ptx::mbar_init(&bars[s], 1);
@@ -359,11 +454,8 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncthreads();
 
-    const int gw = warp * gridDim.x + blockIdx.x;  // consecutive tiles land on different SMs
-    const int NW = gridDim.x * kWarpsPerCta;
+    const int NW = gridDim.x * WARPS;
     const int n_tiles = p.n_strips * p.n_chunks;
-    const int rows_own = p.own_hi - p.own_lo;
-    const int n_bnd = (p.n_chunks > 1 ? 2 : 1) * p.n_strips;
     uint32_t it = 0;
     unsigned long long epoch = 0;
 
@@ -371,52 +463,54 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int par = (p.first_parity + sw) & 1;
         const CUtensorMap* tm_in = par ? &tmB : &tmA;
         T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
-        T* up_out = reinterpret_cast<T*>(p.up_buf[par ^ 1]);
-        T* dn_out = reinterpret_cast<T*>(p.dn_buf[par ^ 1]);
+        T* up_buf_out = reinterpret_cast<T*>(p.up_buf[par ^ 1]);
+        T* dn_buf_out = reinterpret_cast<T*>(p.dn_buf[par ^ 1]);
         const unsigned long long need_up = p.flag_base_up + (unsigned long long)sw * p.n_strips;
         const unsigned long long need_dn = p.flag_base_dn + (unsigned long long)sw * p.n_strips;
         double* partials = p.partials + (size_t)(sw & 1) * n_tiles * 2;
 
-        for (int q = gw; q < n_tiles; q += NW) {
-            if (aborted(p)) break;
-            int chunk, strip;
-            if (q < p.n_strips) {
-                chunk = 0;
-                strip = q;
-            } else if (q < n_bnd) {
-                chunk = p.n_chunks - 1;
-                strip = q - p.n_strips;
-            } else {
-                const int r = q - n_bnd;
-                chunk = 1 + r / p.n_strips;
-                strip = r - (chunk - 1) * p.n_strips;
+        // Dynamic tile queue: one monotonic counter; every warp grabs until it draws a ticket past the end, so
+        // a sweep consumes exactly n_tiles + NW tickets (the host advances ctr_base by that per sweep).
+        const unsigned long long ticket0 = p.ctr_base + (unsigned long long)sw * (unsigned long long)(n_tiles + NW);
+        auto grab = [&]() -> int {
+            unsigned long long v = 0;
+            if (lane == 0) v = atomicAdd(p.tile_ctr, 1ull) - ticket0;
+            v = __shfl_sync(0xffffffffu, v, 0);
+            return v < (unsigned long long)n_tiles ? (int)v : n_tiles;
+        };
+
+        int q = grab();
+        while (q < n_tiles) {
+            const int q_next = grab();  // latency hidden behind this tile
+            if (aborted(p)) {
+                q = q_next;
+                continue;  // keep drawing tickets so the counter stays consistent
             }
-            const int y0 = p.own_lo + (int)((long long)rows_own * chunk / p.n_chunks);
-            const int y1 = p.own_lo + (int)((long long)rows_own * (chunk + 1) / p.n_chunks);
+            int chunk, strip;
+            decode_tile(q, p.n_strips, p.n_chunks, chunk, strip);
+            const int y0 = __ldg(&p.chunk_y[chunk]);
+            const int y1 = __ldg(&p.chunk_y[chunk + 1]);
             const int x_ld = strip * OUTW - M * VEC;
             const bool top = (chunk == 0), bot = (chunk == p.n_chunks - 1);
+            T* up_out = top ? up_buf_out : nullptr;
+            T* dn_out = bot ? dn_buf_out : nullptr;
 
             // Ghost rows this tile reads were written by the neighbour during its previous sweep.
             if (lane == 0) {
                 bool ok = true;
-                if (top && p.up_buf[0] != nullptr) ok = wait_counter_sys(p, &p.my_flags[0], need_up);
-                if (ok && bot && p.dn_buf[0] != nullptr) ok = wait_counter_sys(p, &p.my_flags[1], need_dn);
+                if (up_out != nullptr) ok = wait_counter_sys(p, &p.my_flags[0], need_up);
+                if (ok && dn_out != nullptr) ok = wait_counter_sys(p, &p.my_flags[1], need_dn);
                 ptx::fence_proxy_async();  // peer stores (generic proxy) -> our TMA loads (async proxy)
                 (void)ok;
             }
             __syncwarp();
-            if (aborted(p)) break;
+            if (aborted(p)) {
+                q = q_next;
+                continue;
+            }
 
-            const int gy_lo = p.row0 + y0 - TB, gy_hi = p.row0 + y1 + TB - 1;
-            const bool masked = (gy_lo < p.ylo) || (gy_hi > p.yhi) || (x_ld < p.xlo) ||
-                                (x_ld + 32 * VEC - 1 > p.xhi);
             double rs = 0.0, rm = 0.0;
-            if (masked)
-                process_tile<Op, TB, true, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane,
-                                                rs, rm);
-            else
-                process_tile<Op, TB, false, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it,
-                                                 lane, rs, rm);
+            process_tile<Op, TB, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
 
             if (RES) {
 #pragma unroll
@@ -436,15 +530,16 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // Publish the halo rows this tile pushed: all lanes' peer stores -> one release per neighbour.
             __syncwarp();
             if (lane == 0) {
-                if (top && up_out != nullptr) {
+                if (up_out != nullptr) {
                     ptx::fence_acq_rel_sys();
                     ptx::red_add_release_sys(p.up_flag, 1ull);
                 }
-                if (bot && dn_out != nullptr) {
+                if (dn_out != nullptr) {
                     ptx::fence_acq_rel_sys();
                     ptx::red_add_release_sys(p.dn_flag, 1ull);
                 }
             }
+            q = q_next;
         }
 
         const bool last = (sw + 1 == p.sweeps);
@@ -462,7 +557,7 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (RES && blockIdx.x == 0) {
             // fixed-order reduction of the per-tile partials -> one (sumsq, max) per sweep
             double a = 0.0, b = 0.0;
-            for (int i = threadIdx.x; i < n_tiles; i += kThreads) {
+            for (int i = threadIdx.x; i < n_tiles; i += WARPS * 32) {
                 a += __ldcg(&partials[2 * i]);
                 b = fmax(b, __ldcg(&partials[2 * i + 1]));
             }
@@ -478,7 +573,7 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             __syncthreads();
             if (threadIdx.x == 0) {
                 double sa = 0.0, sb = 0.0;
-                for (int k = 0; k < kThreads / 32; ++k) {
+                for (int k = 0; k < WARPS; ++k) {
                     sa += red_ss[k];
                     sb = fmax(sb, red_mx[k]);
                 }
@@ -511,7 +606,9 @@ struct mcp_fused2d_plan {
     double* partials;
     size_t partials_cap_tiles;
     double* res_out;
-    unsigned long long flag_base_up, flag_base_dn, bar_base;
+    int* chunk_tab;                 // device: kNumTb tables of kMaxChunks + 1 row boundaries
+    std::vector<int> chunk_host[4];  // per time block 1,2,4,8
+    unsigned long long flag_base_up, flag_base_dn, bar_base, ctr_base;
     int res_slots_used;
     int64_t launches;
     unsigned long long timeout_ns;
@@ -532,46 +629,98 @@ int max_tb(int op, int dtype) {
     return dtype == MCP_DTYPE_F64 ? 4 : 8;
 }
 
-void choose_geometry(const mcp_fused2d_plan* pl, int tb, int* n_strips, int* n_chunks) {
+constexpr int kMaxChunks = 4096;
+
+int tb_index(int tb) { return tb == 1 ? 0 : tb == 2 ? 1 : tb == 4 ? 2 : 3; }
+
+// Row-chunk schedule for the dynamic tile queue.  Tiles are drawn in chunk order, so chunk heights follow a
+// guided self-scheduling curve: tall chunks first (the 2*TB redundant pre-roll rows per chunk stay cheap),
+// short chunks last (the tail of a sweep is one *short* tile).  Used for experiments through MCP_GSS_*; the
+// default schedule (build_chunks) is uniform because the measured gain of the taper was within noise.
+void gss_chunks(int rows, int own_lo, int ns, double NW, int tb, int G, double k, int rmin_mult, int rmax_mult,
+                std::vector<int>* out) {
+    std::vector<int>& y = *out;
+    y.clear();
+    y.push_back(own_lo);
+    const int rmin = std::max(G, rmin_mult * tb);
+    const int rmax = std::max(rmin, rmax_mult * tb);
+    int done = 0;
+    while (done < rows) {
+        const int rem = rows - done;
+        int r = (int)((double)rem * ns / (k * NW));  // remaining work ~ k tiles per warp
+        r = std::max(rmin, std::min(rmax, r));
+        // a tile reads r + 2*TB rows in stages of kRowsPerStage: make that a whole number of stages
+        r -= (r + 2 * tb) % kRowsPerStage;
+        if (r < rmin) r += kRowsPerStage;
+        if (rem - r < rmin) r = rem;  // no sliver at the end (every chunk >= ghost depth)
+        if ((int)y.size() >= kMaxChunks) r = rem;
+        done += r;
+        y.push_back(own_lo + done);
+    }
+}
+
+void build_chunks(const mcp_fused2d_plan* pl, int tb, std::vector<int>* out, int* n_strips) {
     const mcp_fused2d_desc& d = pl->d;
     const int outw = outw_rt(d.dtype, tb);
     const int ns = (int)ceil_div(d.w, outw);
-    const int G = d.ghost;
-    const int max_chunks = std::max(1, d.rows_own / std::max(G, 1));
-    int nc;
-    if (d.chunk_rows > 0) {
-        nc = (int)ceil_div(d.rows_own, d.chunk_rows);
-    } else {
-        // Pick the chunk count whose tile count best fills an integer number of waves over all warps
-        // while keeping the 2*TB redundant pre-roll rows per chunk small.
-        const int NW = pl->grid * kWarpsPerCta;
-        double best = -1.0;
-        nc = 1;
-        const int lo = 1, hi = std::min(max_chunks, std::max(1, d.rows_own / 16));
-        for (int c = lo; c <= hi; ++c) {
-            const double tiles = (double)ns * c;
-            const double waves = std::ceil(tiles / NW);
-            const double balance = tiles / (waves * NW);
-            const double rows = (double)d.rows_own / c;
-            const double redundancy = rows / (rows + 2.0 * tb);
-            const double score = balance * redundancy;
-            if (score > best + 1e-9) {
-                best = score;
-                nc = c;
-            }
-        }
-    }
-    nc = std::max(1, std::min(nc, max_chunks));
+    const int G = std::max(d.ghost, 1);
+    const int own_lo = d.ghost;
+    const int rows = d.rows_own;
     *n_strips = ns;
-    *n_chunks = nc;
+    std::vector<int>& y = *out;
+    if (d.chunk_rows > 0) {
+        y.clear();
+        y.push_back(own_lo);
+        const int nc = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(ceil_div(rows, d.chunk_rows),
+                                                                                   std::max(1, rows / G)), kMaxChunks));
+        for (int c = 1; c <= nc; ++c) y.push_back(own_lo + (int)((long long)rows * c / nc));
+        return;
+    }
+    const int NW = pl->grid * warps_for_tb(tb);
+    const char* e_k = getenv("MCP_GSS_K");
+    const char* e_rmin = getenv("MCP_GSS_RMIN");
+    const char* e_rmax = getenv("MCP_GSS_RMAX");
+    if (e_k || e_rmin || e_rmax) {  // manual override for experiments
+        gss_chunks(rows, own_lo, ns, NW, tb, G, e_k ? atof(e_k) : 3.0, e_rmin ? atoi(e_rmin) : 8,
+                   e_rmax ? atoi(e_rmax) : 48, &y);
+        return;
+    }
+    // Two overheads pull in opposite directions: every chunk re-reads and partly recomputes 2*TB pre-roll rows and
+    // refills its TMA pipeline (~(TB + 6) row-times per tile), and the sweep ends with about half a tile of idle
+    // time per warp.  With `share` rows of work per warp, overhead(r) ~ (TB + 6)/r + r/(2*share) is minimal at
+    // r* = sqrt(2*share*(TB + 6)); the measured optimum on B200 follows this within noise (profiles/).
+    const double share = (double)rows * ns / NW;
+    const int rmin = std::max(G, 4 * tb);
+    int r = (int)std::lround(std::sqrt(2.0 * share * (tb + 6)));
+    r = std::max(rmin, std::min(64 * tb, r));
+    r -= (r + 2 * tb) % kRowsPerStage;  // whole number of TMA stages per tile
+    if (r < rmin) r += kRowsPerStage;
+    y.clear();
+    y.push_back(own_lo);
+    int done = 0;
+    while (done < rows) {
+        int take = std::min(r, rows - done);
+        if (rows - done - take < rmin) take = rows - done;  // fold a sliver into the last chunk
+        if ((int)y.size() >= kMaxChunks) take = rows - done;
+        done += take;
+        y.push_back(own_lo + done);
+    }
+}
+
+void choose_geometry(const mcp_fused2d_plan* pl, int tb, int* n_strips, int* n_chunks) {
+    const std::vector<int>& y = pl->chunk_host[tb_index(tb)];
+    *n_strips = (int)ceil_div(pl->d.w, outw_rt(pl->d.dtype, tb));
+    *n_chunks = (int)y.size() - 1;
 }
 
 template <class Op, int TB>
 int launch_variant(mcp_fused2d_plan* pl, const Fused2dParams& p, bool res, cudaStream_t stream) {
+    constexpr int W = warps_for_tb(TB);
+    constexpr int smem = smem_bytes_for(W);
     void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
-    const void* fn = res ? (const void*)fused2d_kernel<Op, TB, true> : (const void*)fused2d_kernel<Op, TB, false>;
-    MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(pl->grid), dim3(kThreads), args, kSmemBytes, stream));
+    const void* fn = res ? (const void*)fused2d_kernel<Op, TB, true, W> : (const void*)fused2d_kernel<Op, TB, false, W>;
+    MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(pl->grid), dim3(W * 32), args, smem, stream));
     pl->launches++;
     return MCP_OK;
 }
@@ -628,7 +777,7 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->d = d;
     pl->rows_alloc = d.rows_own + 2 * d.ghost;
     pl->parity = 0;
-    pl->flag_base_up = pl->flag_base_dn = pl->bar_base = 0;
+    pl->flag_base_up = pl->flag_base_dn = pl->bar_base = pl->ctr_base = 0;
     pl->res_slots_used = 0;
     pl->launches = 0;
     pl->timeout_ns = 20ull * 1000000000ull;
@@ -637,6 +786,7 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->status = nullptr;
     pl->partials = nullptr;
     pl->res_out = nullptr;
+    pl->chunk_tab = nullptr;
 
     int rc = device_sm_count(&pl->sm_count);
     if (rc) { delete pl; return rc; }
@@ -666,6 +816,23 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         mcp_fused2d_destroy(pl);
         return MCP_ERR_CUDA;
     }
+    if ((e = cudaMalloc(&pl->chunk_tab, 4 * (kMaxChunks + 1) * sizeof(int))) != cudaSuccess) {
+        set_error("mcp_fused2d_create: chunk table allocation failed: %s", cudaGetErrorString(e));
+        mcp_fused2d_destroy(pl);
+        return MCP_ERR_CUDA;
+    }
+    for (int tb = 1; tb <= 8; tb *= 2) {
+        int ns = 0;
+        std::vector<int>& y = pl->chunk_host[tb_index(tb)];
+        build_chunks(pl, tb, &y, &ns);
+        e = cudaMemcpy(pl->chunk_tab + tb_index(tb) * (kMaxChunks + 1), y.data(), y.size() * sizeof(int),
+                       cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            set_error("mcp_fused2d_create: chunk table upload failed: %s", cudaGetErrorString(e));
+            mcp_fused2d_destroy(pl);
+            return MCP_ERR_CUDA;
+        }
+    }
     *plan_out = pl;
     return MCP_OK;
 }
@@ -678,8 +845,16 @@ int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_stri
     if (n_strips) *n_strips = ns;
     if (n_chunks) *n_chunks = nc;
     if (grid) *grid = pl->grid;
-    if (smem_bytes) *smem_bytes = kSmemBytes;
+    if (smem_bytes) *smem_bytes = smem_bytes_for(warps_for_tb(time_block));
     return MCP_OK;
+}
+
+int mcp_fused2d_chunks(const mcp_fused2d_plan* pl, int time_block, int* rows_out, int max_entries) {
+    MCP_REQUIRE(pl && rows_out, "null argument");
+    const std::vector<int>& y = pl->chunk_host[tb_index(time_block)];
+    const int n = std::min((int)y.size() - 1, max_entries);
+    for (int i = 0; i < n; ++i) rows_out[i] = y[i + 1] - y[i];
+    return n;
 }
 
 int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int residual_mode, void* stream_) {
@@ -713,9 +888,12 @@ int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int r
         p.up_flag = (unsigned long long*)d.up_flag;
         p.dn_flag = (unsigned long long*)d.dn_flag;
         p.grid_bar = pl->grid_bar;
+        p.tile_ctr = pl->grid_bar + 16;  // separate 128-byte line of the same zeroed allocation
+        p.ctr_base = pl->ctr_base;
         p.status = pl->status;
         p.partials = pl->partials;
         p.res_out = pl->res_out;
+        p.chunk_y = pl->chunk_tab + tb_index(tb) * (kMaxChunks + 1);
         p.flag_base_up = pl->flag_base_up;
         p.flag_base_dn = pl->flag_base_dn;
         p.bar_base = pl->bar_base;
@@ -742,6 +920,7 @@ int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int r
 
         const unsigned long long barriers = res ? (unsigned long long)sweeps : (unsigned long long)(sweeps - 1);
         pl->bar_base += barriers * (unsigned long long)pl->grid;
+        pl->ctr_base += (unsigned long long)sweeps * (unsigned long long)((long long)ns * nc + (long long)pl->grid * warps_for_tb(tb));
         pl->flag_base_up += (unsigned long long)sweeps * ns;
         pl->flag_base_dn += (unsigned long long)sweeps * ns;
         pl->parity = (pl->parity + sweeps) & 1;
@@ -788,6 +967,7 @@ int mcp_fused2d_destroy(mcp_fused2d_plan* pl) {
     if (pl->status) cudaFree(pl->status);
     if (pl->partials) cudaFree(pl->partials);
     if (pl->res_out) cudaFree(pl->res_out);
+    if (pl->chunk_tab) cudaFree(pl->chunk_tab);
     delete pl;
     return MCP_OK;
 }
