@@ -26,6 +26,11 @@ extern "C" {
 #define MCP_OP_MDF 0  /* 2-D 5-point heat/Jacobi update, M:10-22 */
 #define MCP_OP_LIFE 1 /* Game of Life B3/S23, K:10-68 */
 
+#define MCP_MAX_RANKS 16
+#define MCP_RES_RING 64
+#define MCP_NORM_LINF 1
+#define MCP_NORM_L2 2
+
 /* residual modes of the fused kernel */
 #define MCP_RES_NONE 0
 #define MCP_RES_LAST 1 /* residual of the last generation of every time block */
@@ -94,6 +99,15 @@ typedef struct mcp_fused2d_desc {
     int ylo, yhi, xlo, xhi; /* cells outside this inclusive global box keep their value */
     int chunk_rows;  /* rows per tile (0 = choose) */
     int max_ctas;    /* 0 = one CTA per SM */
+    /* Fused global residual all-reduce over NVLink (optional; world <= 1 or res_inbox == NULL = local only).
+     * Every rank owns an inbox ring of MCP_RES_RING x MCP_MAX_RANKS (sumsq, max) pairs and an arrival counter,
+     * both zeroed, and passes the addresses of ALL ranks' inboxes/counters (its own included) mapped into this
+     * process.  Results are summed in rank order, so every rank obtains the same bits. */
+    int world, rank;
+    double* res_inbox;                        /* local ring */
+    uint64_t* res_flag;                       /* local arrival counter */
+    double* peer_res_inbox[MCP_MAX_RANKS];    /* [r] = rank r's ring as seen from here */
+    uint64_t* peer_res_flag[MCP_MAX_RANKS];   /* [r] = rank r's counter as seen from here */
 } mcp_fused2d_desc;
 
 typedef struct mcp_fused2d_plan mcp_fused2d_plan;
@@ -101,10 +115,17 @@ typedef struct mcp_fused2d_plan mcp_fused2d_plan;
 int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out);
 /* Advance `generations` generations; the state ends in buffer mcp_fused2d_parity(plan). */
 int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int residual_mode, void* stream);
+/* Run-to-tolerance in ONE launch: advance until the global residual of a time block's last generation satisfies
+ * max|u'-u| <= tol (MCP_NORM_LINF) or ||u'-u||_2 <= tol (MCP_NORM_L2), at most max_generations.  The decision is
+ * taken on the device from the fused all-reduce; the run ends one time block after the block that converged.
+ * Synchronises the stream (the executed count is a device result).  Extension: the reference has a fixed
+ * generation count only (M:153,157,186). */
+int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* plan, int max_generations, int time_block, int norm, double tol,
+                                 int* generations_done, void* stream);
 int mcp_fused2d_parity(const mcp_fused2d_plan* plan);
 int mcp_fused2d_set_parity(mcp_fused2d_plan* plan, int parity);
-/* Local residual history of the last run with MCP_RES_LAST: per time block (sum of squares, max abs) of
- * u' - u over this rank's owned cells.  Returns the number of entries written (<= max_entries). */
+/* Residual history of the last run with MCP_RES_LAST: per time block (sum of squares, max abs) of u' - u --
+ * global over all ranks when the descriptor enabled the fused all-reduce, else over this rank's owned cells.  Returns the number of entries written (<= max_entries). */
 int mcp_fused2d_residuals(mcp_fused2d_plan* plan, double* sumsq_max_pairs, int max_entries);
 /* 0 = healthy; otherwise the MCP_ERR_* code a kernel recorded (e.g. halo-flag wait timeout). */
 int mcp_fused2d_status(mcp_fused2d_plan* plan);

@@ -35,6 +35,9 @@ class FusedDesc(C.Structure):
         ("flags", C.c_void_p), ("up_flag", C.c_void_p), ("dn_flag", C.c_void_p),
         ("ylo", C.c_int), ("yhi", C.c_int), ("xlo", C.c_int), ("xhi", C.c_int),
         ("chunk_rows", C.c_int), ("max_ctas", C.c_int),
+        ("world", C.c_int), ("rank", C.c_int),
+        ("res_inbox", C.c_void_p), ("res_flag", C.c_void_p),
+        ("peer_res_inbox", C.c_void_p * 16), ("peer_res_flag", C.c_void_p * 16),
     ]
 
 
@@ -72,6 +75,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_step3d.argtypes = [i, vp, vp, i64, i64, i, i, i, i, i, i, i, i, i, i, i, dbl, vp]
     lib.mcp_fused2d_create.argtypes = [C.POINTER(FusedDesc), c_void_pp]
     lib.mcp_fused2d_run.argtypes = [vp, i, i, i, vp]
+    lib.mcp_fused2d_run_to_tolerance.argtypes = [vp, i, i, i, dbl, C.POINTER(i), vp]
     lib.mcp_fused2d_parity.argtypes = [vp]
     lib.mcp_fused2d_set_parity.argtypes = [vp, i]
     lib.mcp_fused2d_residuals.argtypes = [vp, vp, i]

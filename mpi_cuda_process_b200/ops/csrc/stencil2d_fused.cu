@@ -48,7 +48,9 @@ constexpr int kSmemBytes = smem_bytes_for(kWarpsPerCta);
 // TB = 8 keeps 96 registers of row windows per thread: run 12 warps x 168 registers instead of 16 x 128.
 constexpr int kWarpsTb8 = 8;
 __host__ __device__ constexpr int warps_for_tb(int tb) { return tb >= 8 ? kWarpsTb8 : kWarpsPerCta; }
-constexpr int kMaxResSlots = 4096;
+constexpr int kMaxResSlots = 16384;
+constexpr int kMaxRanks = MCP_MAX_RANKS;
+constexpr int kResRing = MCP_RES_RING;
 
 struct Fused2dParams {
     void* buf[2];
@@ -63,6 +65,17 @@ struct Fused2dParams {
     double* partials;  // [2][n_tiles][2]
     double* res_out;   // [kMaxResSlots][2]
     const int* chunk_y;  // [n_chunks + 1] local row boundaries of the row chunks (host-built schedule)
+    // cross-rank residual all-reduce over NVLink: every rank stores its (sumsq, max) into slot [seq % ring][rank] of
+    // every rank's inbox, bumps that rank's arrival counter, then sums its own inbox in rank order
+    double* peer_inbox[kMaxRanks];
+    unsigned long long* peer_res_flag[kMaxRanks];
+    const unsigned long long* res_flag;
+    unsigned long long res_seq_base;
+    int* stop_word;    // 0 = keep going, else total number of sweeps this launch executes
+    int* sweeps_done;  // sweeps actually executed by this launch
+    double stop_thresh;
+    int stop_mode;  // 0 none, 1: stop when max|d| <= thresh, 2: stop when sum d^2 <= thresh
+    int world, rank;
     unsigned long long flag_base_up, flag_base_dn;
     unsigned long long bar_base;
     unsigned long long ctr_base;
@@ -459,7 +472,13 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint32_t it = 0;
     unsigned long long epoch = 0;
 
+    int executed = 0;
     for (int sw = 0; sw < p.sweeps; ++sw) {
+        if (RES && p.stop_mode != 0 && sw > 0) {
+            // decided by CTA 0 from the global residual of sweep sw-2 and published before barrier sw-1
+            const int s = *((volatile int*)p.stop_word);
+            if (s != 0 && sw >= s) break;
+        }
         const int par = (p.first_parity + sw) & 1;
         const CUtensorMap* tm_in = par ? &tmB : &tmA;
         T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
@@ -577,15 +596,44 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     sa += red_ss[k];
                     sb = fmax(sb, red_mx[k]);
                 }
+                if (p.world > 1 && p.peer_inbox[0] != nullptr) {
+                    // all-reduce over peer memory: push, signal, wait for everybody, sum in rank order
+                    const unsigned long long seq = p.res_seq_base + (unsigned long long)sw;
+                    const size_t off = ((size_t)(seq % kResRing) * kMaxRanks + (size_t)p.rank) * 2;
+                    for (int r = 0; r < p.world; ++r) {
+                        p.peer_inbox[r][off] = sa;
+                        p.peer_inbox[r][off + 1] = sb;
+                    }
+                    ptx::fence_acq_rel_sys();
+                    for (int r = 0; r < p.world; ++r) ptx::red_add_release_sys(p.peer_res_flag[r], 1ull);
+                    if (wait_counter_sys(p, p.res_flag, (seq + 1ull) * (unsigned long long)p.world)) {
+                        const volatile double* in = p.peer_inbox[p.rank] + (size_t)(seq % kResRing) * kMaxRanks * 2;
+                        sa = 0.0;
+                        sb = 0.0;
+                        for (int r = 0; r < p.world; ++r) {
+                            sa += in[2 * r];
+                            sb = fmax(sb, in[2 * r + 1]);
+                        }
+                    }
+                }
                 const int slot = p.res_slot0 + sw;
                 if (slot < kMaxResSlots) {
                     p.res_out[2 * slot] = sa;
                     p.res_out[2 * slot + 1] = sb;
                 }
+                if (p.stop_mode != 0 && *((volatile int*)p.stop_word) == 0) {
+                    const bool conv = p.stop_mode == 1 ? (sb <= p.stop_thresh) : (sa <= p.stop_thresh);
+                    if (conv) {
+                        *((volatile int*)p.stop_word) = sw + 2;  // one more sweep runs while this is published
+                        __threadfence();
+                    }
+                }
             }
             __syncthreads();
         }
+        executed = sw + 1;
     }
+    if (RES && blockIdx.x == 0 && threadIdx.x == 0) *p.sweeps_done = executed;
 }
 
 // ------------------------------------------------------------------------------------------ host plan
@@ -607,6 +655,9 @@ struct mcp_fused2d_plan {
     size_t partials_cap_tiles;
     double* res_out;
     int* chunk_tab;                 // device: kNumTb tables of kMaxChunks + 1 row boundaries
+    int* stop_words;                // device: [0] stop word, [1] sweeps done
+    unsigned long long res_seq;     // sweeps whose residual has been exchanged so far
+    int last_generations;           // generations executed by the last run call
     std::vector<int> chunk_host[4];  // per time block 1,2,4,8
     unsigned long long flag_base_up, flag_base_dn, bar_base, ctr_base;
     int res_slots_used;
@@ -787,6 +838,9 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->partials = nullptr;
     pl->res_out = nullptr;
     pl->chunk_tab = nullptr;
+    pl->stop_words = nullptr;
+    pl->res_seq = 0;
+    pl->last_generations = 0;
 
     int rc = device_sm_count(&pl->sm_count);
     if (rc) { delete pl; return rc; }
@@ -813,6 +867,11 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         (e = cudaMalloc(&pl->res_out, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
         (e = cudaMemset(pl->res_out, 0, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess) {
         set_error("mcp_fused2d_create: scratch allocation failed: %s", cudaGetErrorString(e));
+        mcp_fused2d_destroy(pl);
+        return MCP_ERR_CUDA;
+    }
+    if ((e = cudaMalloc(&pl->stop_words, 256)) != cudaSuccess || (e = cudaMemset(pl->stop_words, 0, 256)) != cudaSuccess) {
+        set_error("mcp_fused2d_create: stop word allocation failed: %s", cudaGetErrorString(e));
         mcp_fused2d_destroy(pl);
         return MCP_ERR_CUDA;
     }
@@ -857,17 +916,15 @@ int mcp_fused2d_chunks(const mcp_fused2d_plan* pl, int time_block, int* rows_out
     return n;
 }
 
-int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int residual_mode, void* stream_) {
-    MCP_REQUIRE(pl, "null plan");
-    MCP_REQUIRE(generations >= 0, "negative generation count");
+static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool res, int stop_mode,
+                    double stop_thresh, cudaStream_t stream) {
     const mcp_fused2d_desc& d = pl->d;
     const int tbmax = std::min(max_tb(d.op, d.dtype), d.ghost);
-    MCP_REQUIRE(time_block >= 1, "time_block must be >= 1");
     int tb = 1;
     while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    const bool res = residual_mode != MCP_RES_NONE;
     if (res) pl->res_slots_used = 0;
+    pl->last_generations = 0;
+    const bool exchange = d.world > 1 && d.res_inbox != nullptr;
 
     int remaining = generations;
     while (remaining > 0) {
@@ -914,20 +971,69 @@ int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int r
         p.first_parity = pl->parity;
         p.res_slot0 = pl->res_slots_used;
         p.debug_flags = pl->debug_flags;
+        p.world = d.world > 0 ? d.world : 1;
+        p.rank = d.rank;
+        p.res_flag = (const unsigned long long*)d.res_flag;
+        p.res_seq_base = pl->res_seq;
+        if (exchange)
+            for (int r = 0; r < p.world; ++r) {
+                p.peer_inbox[r] = (double*)d.peer_res_inbox[r];
+                p.peer_res_flag[r] = (unsigned long long*)d.peer_res_flag[r];
+            }
+        p.stop_word = pl->stop_words;
+        p.sweeps_done = pl->stop_words + 1;
+        p.stop_mode = stop_mode;
+        p.stop_thresh = stop_thresh;
+        if (stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(pl->stop_words, 0, 2 * sizeof(int), stream));
 
         int rc = launch_any(pl, tb, p, res, stream);
         if (rc) return rc;
 
-        const unsigned long long barriers = res ? (unsigned long long)sweeps : (unsigned long long)(sweeps - 1);
+        int executed = sweeps;
+        if (stop_mode != 0) {
+            // the number of sweeps that ran is decided on the device: wait for it before touching the counters
+            MCP_CUDA_TRY(cudaStreamSynchronize(stream));
+            int words[2] = {0, 0};
+            MCP_CUDA_TRY(cudaMemcpy(words, pl->stop_words, sizeof(words), cudaMemcpyDeviceToHost));
+            executed = words[1];
+            MCP_REQUIRE(executed >= 0 && executed <= sweeps, "device reported %d executed sweeps of %d", executed, sweeps);
+        }
+        const unsigned long long barriers = res ? (unsigned long long)executed : (unsigned long long)(executed - 1);
         pl->bar_base += barriers * (unsigned long long)pl->grid;
-        pl->ctr_base += (unsigned long long)sweeps * (unsigned long long)((long long)ns * nc + (long long)pl->grid * warps_for_tb(tb));
-        pl->flag_base_up += (unsigned long long)sweeps * ns;
-        pl->flag_base_dn += (unsigned long long)sweeps * ns;
-        pl->parity = (pl->parity + sweeps) & 1;
-        if (res) pl->res_slots_used = std::min(kMaxResSlots, pl->res_slots_used + sweeps);
+        pl->ctr_base += (unsigned long long)executed *
+                        (unsigned long long)((long long)ns * nc + (long long)pl->grid * warps_for_tb(tb));
+        pl->flag_base_up += (unsigned long long)executed * ns;
+        pl->flag_base_dn += (unsigned long long)executed * ns;
+        pl->parity = (pl->parity + executed) & 1;
+        if (res) {
+            pl->res_slots_used = std::min(kMaxResSlots, pl->res_slots_used + executed);
+            if (exchange) pl->res_seq += (unsigned long long)executed;
+        }
+        pl->last_generations += executed * tb;
+        if (stop_mode != 0) break;  // tolerance runs use one block size; the caller decides how to continue
         remaining -= sweeps * tb;
     }
     return MCP_OK;
+}
+
+int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int residual_mode, void* stream_) {
+    MCP_REQUIRE(pl, "null plan");
+    MCP_REQUIRE(generations >= 0, "negative generation count");
+    MCP_REQUIRE(time_block >= 1, "time_block must be >= 1");
+    return run_impl(pl, generations, time_block, residual_mode != MCP_RES_NONE, 0, 0.0, (cudaStream_t)stream_);
+}
+
+int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int time_block, int norm, double tol,
+                                 int* generations_done, void* stream_) {
+    MCP_REQUIRE(pl, "null plan");
+    MCP_REQUIRE(max_generations >= 1 && time_block >= 1, "bad generation count or time block");
+    MCP_REQUIRE(norm == MCP_NORM_LINF || norm == MCP_NORM_L2, "norm must be MCP_NORM_LINF or MCP_NORM_L2");
+    MCP_REQUIRE(tol >= 0.0, "negative tolerance");
+    const double thresh = norm == MCP_NORM_L2 ? tol * tol : tol;  // the kernel compares the sum of squares
+    int rc = run_impl(pl, max_generations, time_block, true, norm == MCP_NORM_LINF ? 1 : 2, thresh,
+                      (cudaStream_t)stream_);
+    if (generations_done) *generations_done = pl->last_generations;
+    return rc;
 }
 
 int mcp_fused2d_parity(const mcp_fused2d_plan* pl) { return pl ? pl->parity : 0; }
@@ -968,6 +1074,7 @@ int mcp_fused2d_destroy(mcp_fused2d_plan* pl) {
     if (pl->partials) cudaFree(pl->partials);
     if (pl->res_out) cudaFree(pl->res_out);
     if (pl->chunk_tab) cudaFree(pl->chunk_tab);
+    if (pl->stop_words) cudaFree(pl->stop_words);
     delete pl;
     return MCP_OK;
 }

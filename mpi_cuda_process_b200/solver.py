@@ -140,9 +140,14 @@ class Solver:
             for n in max_own[:-1]:
                 max_alloc *= n + 2 * G
             self._buf_bytes = _round_up(max_alloc * self.pitch * self.esize, 4096)
-            self._flags_bytes = 4096
+            # signalling pad in front of the buffers: halo counters @0, residual arrival counter @256,
+            # residual inbox ring (64 slots x 16 ranks x 16 B) @4096
+            self._flags_bytes = 32768
             need_peers = self.backend == "fused" and self.ctx.distributed
-            peers = [r for pair in self.block.neighbors for r in pair if r is not None] if need_peers else []
+            # halo pushes need the two neighbours; the fused residual all-reduce stores to every rank
+            peers = list(range(self.ctx.world)) if need_peers else []
+            if need_peers and self.ctx.world > 16:
+                raise ValueError("the fused backend supports up to 16 ranks (MCP_MAX_RANKS)")
             total = self._flags_bytes + 2 * self._buf_bytes
             if need_peers:
                 self._arena = SymmetricArena(self.ctx, total, peers=peers)
@@ -185,6 +190,15 @@ class Solver:
         d.ylo, d.yhi, d.xlo, d.xhi = self._fix_bounds
         d.chunk_rows = int(cfg.extra.get("chunk_rows", 0))
         d.max_ctas = int(cfg.extra.get("max_ctas", 0))
+        d.world, d.rank = self.ctx.world, self.ctx.rank
+        self._res_in_kernel = False
+        if self.ctx.distributed and not cfg.extra.get("host_residual", False):
+            d.res_inbox = self._arena.peer_ptr(self.ctx.rank, 4096)
+            d.res_flag = self._arena.peer_ptr(self.ctx.rank, 256)
+            for r in range(self.ctx.world):
+                d.peer_res_inbox[r] = self._arena.peer_ptr(r, 4096)
+                d.peer_res_flag[r] = self._arena.peer_ptr(r, 256)
+            self._res_in_kernel = True
         plan = C.c_void_p()
         _lib.check(self._lib.mcp_fused2d_create(C.byref(d), C.byref(plan)), "mcp_fused2d_create")
         self._plan = plan
@@ -273,6 +287,40 @@ class Solver:
         self.bufs[self.cur].copy_(local, non_blocking=non_blocking)
         self._ghosts_valid = True
 
+    def stage_input(self, local: torch.Tensor) -> None:
+        """Start an asynchronous upload of the NEXT input slab (pinned host memory, shape ``store_shape``) on a
+        side stream into a device staging buffer; it overlaps whatever the solver is computing.  Pair with
+        :meth:`commit_input`."""
+        if tuple(local.shape) != tuple(self.store_shape):
+            raise ValueError(f"local shape {tuple(local.shape)} != {self.store_shape}")
+        if not self.ctx.is_cuda:
+            self._staged = local.clone()
+            return
+        if getattr(self, "_stage_buf", None) is None:
+            self._stage_buf = torch.empty(self.store_shape, dtype=self.tdtype, device=self.ctx.device)
+            self._copy_stream = torch.cuda.Stream(device=self.ctx.device)
+            self._stage_done = torch.cuda.Event()
+            self._stage_free = torch.cuda.Event()
+            self._stage_free.record()
+        self._copy_stream.wait_event(self._stage_free)          # previous commit has consumed the staging buffer
+        with torch.cuda.stream(self._copy_stream):
+            self._stage_buf.copy_(local, non_blocking=True)
+            self._stage_done.record(self._copy_stream)
+
+    def commit_input(self) -> None:
+        """Make the staged slab the current state (device-to-device copy once the upload has landed)."""
+        if not self.ctx.is_cuda:
+            self.bufs[self.cur].copy_(self._staged)
+            self._ghosts_valid = True
+            return
+        if self.backend == "fused" and self.ctx.distributed:
+            self.ctx.barrier()      # neighbours' last halo pushes of the previous run must have landed first
+        cur = torch.cuda.current_stream(self.ctx.device)
+        cur.wait_event(self._stage_done)
+        self.bufs[self.cur].copy_(self._stage_buf, non_blocking=True)
+        self._stage_free.record(cur)
+        self._ghosts_valid = True
+
     def _reset_plan_parity(self):
         if self._plan is not None:
             from .ops import _lib
@@ -326,22 +374,25 @@ class Solver:
             self._collect_fused_residual(st)
 
     def _collect_fused_residual(self, st: RunStats) -> None:
-        buf = (C.c_double * (2 * 4096))()
-        n = self._lib.mcp_fused2d_residuals(self._plan, buf, 4096)
+        buf = (C.c_double * (2 * 16384))()
+        n = self._lib.mcp_fused2d_residuals(self._plan, buf, 16384)
         from .ops import _lib
         _lib.check(n, "mcp_fused2d_residuals")
         status = self._lib.mcp_fused2d_status(self._plan)
         _lib.check(status, "fused kernel status")
         local = [(buf[2 * i], buf[2 * i + 1]) for i in range(n)]
-        allr = self.ctx.all_gather_object(local)
-        hist = []
-        for i in range(n):
-            ss = 0.0
-            mx = 0.0
-            for r in range(self.ctx.world):     # fixed rank order -> same bits everywhere
-                ss += allr[r][i][0]
-                mx = max(mx, allr[r][i][1])
-            hist.append((ss, mx))
+        if getattr(self, "_res_in_kernel", False) or not self.ctx.distributed:
+            hist = local                        # already global: all-reduced inside the kernel over NVLink
+        else:
+            allr = self.ctx.all_gather_object(local)
+            hist = []
+            for i in range(n):
+                ss = 0.0
+                mx = 0.0
+                for r in range(self.ctx.world):     # fixed rank order -> same bits everywhere
+                    ss += allr[r][i][0]
+                    mx = max(mx, allr[r][i][1])
+                hist.append((ss, mx))
         if hist:
             self._last_residual = hist[-1]
         kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
@@ -535,6 +586,8 @@ class Solver:
             every = max(self.time_block, every // self.time_block * self.time_block)
         total = RunStats(cells=self.cfg.cells)
         kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+        if self.backend == "fused" and not self.cfg.extra.get("host_tolerance_loop", False):
+            return self._run_to_tolerance_fused(tol, max_g, kind)
         while total.generations < max_g:
             n = min(every, max_g - total.generations)
             if self.backend == "fused":
@@ -563,6 +616,36 @@ class Solver:
             if r <= tol:
                 break
         return total
+
+    def _run_to_tolerance_fused(self, tol: float, max_g: int, kind: str) -> RunStats:
+        """One launch: the kernel all-reduces the residual of every time block over NVLink and stops itself."""
+        from .ops import _lib
+        self._ensure_plan()
+        tb = self.time_block
+        max_g = max(tb, max_g // tb * tb)
+        max_g = min(max_g, 16384 * tb)
+        st = RunStats(cells=self.cfg.cells)
+        done = C.c_int(0)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        before = self._lib.mcp_fused2d_launches(self._plan)
+        ev0.record()
+        _lib.check(self._lib.mcp_fused2d_run_to_tolerance(self._plan, max_g, tb, 2 if kind == "l2" else 1, float(tol),
+                                                          C.byref(done), self._stream()),
+                   "mcp_fused2d_run_to_tolerance")
+        ev1.record()
+        ev1.synchronize()
+        st.device_ms = self.ctx.all_reduce_max(ev0.elapsed_time(ev1))
+        st.launches = int(self._lib.mcp_fused2d_launches(self._plan) - before)
+        st.generations = int(done.value)
+        self.cur = self._lib.mcp_fused2d_parity(self._plan)
+        base = self.generation
+        self._collect_fused_residual(st)
+        st.residual_history = [(base + (i + 1) * tb, r) for i, (_, r) in enumerate(st.residual_history)]
+        self.generation += st.generations
+        self.total_stats.generations += st.generations
+        self.total_stats.device_ms += st.device_ms
+        self.total_stats.launches += st.launches
+        return st
 
     def residual(self) -> Optional[float]:
         """Last computed global residual (according to ``cfg.residual``), or None."""

@@ -81,6 +81,33 @@ def main() -> int:
                 print(json.dumps({"case": "fused residual", "world": ctx.world, "equal_on_all_ranks": ok}), flush=True)
             if not ok:
                 rc = 1
+    # run-to-tolerance in one launch, decision taken on the device from the NVLink all-reduce (fp64, l2 norm)
+    if rc == 0:
+        cfg = RunConfig(workload="mdf", height=96, width=80, backend="fused", time_block=4, dtype="fp64",
+                        residual="l2", tol=0.5, max_generations=4000)
+        with Solver(cfg, ctx=ctx) as s:
+            s.initialize()
+            st = s.run_to_tolerance()
+            s.check_status()
+            got = s.gather()
+            u = oracle.mdf_init(96, 80, dtype=np.float64)
+            gen, conv = 0, None
+            while conv is None and gen < 4000:
+                v = oracle.mdf_step(u)
+                gen += 1
+                if gen % 4 == 0 and oracle.residual(v, u, "l2") <= 0.5:
+                    conv = gen
+                u = v
+            same_everywhere = len(set(ctx.all_gather_object((st.generations, tuple(st.residual_history))))) == 1
+            ok = same_everywhere and st.launches == 1 and st.generations == conv + 4
+            if ctx.rank == 0:
+                ref = oracle.mdf_run(oracle.mdf_init(96, 80, dtype=np.float64), st.generations)
+                ok = ok and got.tobytes() == ref.tobytes()
+                print(json.dumps({"case": "fused run-to-tolerance fp64 l2", "world": ctx.world, "generations": st.generations,
+                                  "expected": conv + 4, "launches": st.launches, "ok": bool(ok)}), flush=True)
+            ok = ctx.broadcast_object(ok, 0)
+            if not ok:
+                rc = 1
     ctx.close()
     return rc
 

@@ -255,3 +255,31 @@ def test_cli_on_gpu():
                        input="100 256 256\n", capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr + r.stdout
     assert "bitwise equal after 100 generations" in r.stdout and '"backend": "fused"' in r.stdout
+
+
+def test_fused_run_to_tolerance_single_launch():
+    """The kernel stops itself from the fused residual: one launch, one time block after convergence."""
+    h, w, tb, tol = 64, 96, 4, 0.05
+    cfg = RunConfig(workload="mdf", height=h, width=w, backend="fused", time_block=tb, tol=tol, max_generations=4000)
+    with Solver(cfg) as s:
+        s.initialize()
+        st = s.run_to_tolerance()
+        s.check_status()
+        assert st.launches == 1
+        # oracle: first block whose last generation has max|d| <= tol; the run ends one block later
+        u = oracle.mdf_init(h, w)
+        gen, conv = 0, None
+        while conv is None:
+            v = oracle.mdf_step(u)
+            gen += 1
+            if gen % tb == 0 and oracle.residual(v, u, "linf") <= tol:
+                conv = gen
+            u = v
+        assert st.generations == conv + tb
+        assert s.generation == st.generations
+        assert s.gather().tobytes() == oracle.mdf_run(oracle.mdf_init(h, w), st.generations).tobytes()
+        hist = dict(st.residual_history)
+        assert hist[conv] <= tol and all(r > tol for g_, r in st.residual_history if g_ < conv)
+        # the solver can keep going afterwards (counters stayed consistent)
+        s.run(8)
+        assert s.gather().tobytes() == oracle.mdf_run(oracle.mdf_init(h, w), st.generations + 8).tobytes()
