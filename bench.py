@@ -37,7 +37,7 @@ def parse_args(argv=None):
     p.add_argument("--impl", default="fused", choices=["fused", "ours", "reference", "nccl", "staged"])
     p.add_argument("--height", type=int, default=16384)
     p.add_argument("--width", type=int, default=16384)
-    p.add_argument("--gens-per-step", type=int, default=100)
+    p.add_argument("--gens-per-step", type=int, default=1000)
     p.add_argument("--time-block", type=int, default=8)
     p.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])
     p.add_argument("--scaling", default="strong", choices=["strong", "weak"],

@@ -26,6 +26,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <cmath>
 #include <new>
 #include <vector>
@@ -48,6 +49,10 @@ constexpr int kSmemBytes = smem_bytes_for(kWarpsPerCta);
 // TB = 8 keeps 96 registers of row windows per thread: run 12 warps x 168 registers instead of 16 x 128.
 constexpr int kWarpsTb8 = 8;
 __host__ __device__ constexpr int warps_for_tb(int tb) { return tb >= 8 ? kWarpsTb8 : kWarpsPerCta; }
+// Life keeps cells and horizontal sums per window row (24 registers per level): TB = 4 also needs the wide budget.
+__host__ __device__ constexpr int warps_for(bool is_life, int tb) {
+    return (is_life && tb >= 4) ? kWarpsTb8 : warps_for_tb(tb);
+}
 constexpr int kMaxResSlots = 16384;
 constexpr int kMaxRanks = MCP_MAX_RANKS;
 constexpr int kResRing = MCP_RES_RING;
@@ -61,6 +66,7 @@ struct Fused2dParams {
     unsigned long long* dn_flag;
     unsigned long long* grid_bar;
     unsigned long long* tile_ctr;
+    unsigned* tile_done;  // [n_tiles] last sweep (1-based, within this launch) each tile has completed
     int* status;
     double* partials;  // [2][n_tiles][2]
     double* res_out;   // [kMaxResSlots][2]
@@ -88,6 +94,7 @@ struct Fused2dParams {
     int n_strips, n_chunks;
     int sweeps, first_parity, res_slot0;
     int debug_flags;
+    int sync_mode;  // 1 = grid barrier between sweeps, 2 = per-tile dataflow flags (no barrier)
 };
 
 // ------------------------------------------------------------------------------------------ operators
@@ -283,15 +290,17 @@ __device__ __forceinline__ uint4 ld_global_v4(const void* p) {
 }
 
 // One shared-memory stage = kRowsPerStage input rows pushed through the TB-level register wavefront.
-// GENERAL: cells may be fixed (boundary masks) and some output rows may fall outside [y0, y1).
-// !GENERAL: the lean path used by almost every iteration -- no masks, no range checks, no branches.
-template <class Op, int TB, bool GENERAL, bool RES>
+// MODE 0: the lean path used by almost every iteration -- no masks, no range checks, no branches.
+// MODE 1: edge strips away from the top/bottom of the tile: per-lane column masks only (fixed ring / pad columns).
+// MODE 2: general: row and column masks, output rows may fall outside [y0, y1), useless pre-roll levels skipped.
+template <class Op, int TB, int MODE, bool RES>
 __device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const uint8_t* sp,
                                            typename Op::T*& optr, const long long pitch, const int cbase,
                                            const int n_in, const int gy_base, const int ylo, const int yhi,
                                            const unsigned colfix, const bool lane_valid, const bool lane_store,
                                            double& rs, double& rm) {
     using V = typename Op::V;
+    constexpr bool GENERAL = (MODE == 2);
 #pragma unroll
     for (int j = 0; j < kRowsPerStage; ++j) {
         L[0][mod3(j)] = Op::make_row(bitcast_v<V>(ptx::ld_shared_v4(sp + j * kRowBytes)));
@@ -306,6 +315,8 @@ __device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const u
                 const int gy = gy_base + j - t;
                 const unsigned m = (gy < ylo || gy > yhi) ? 0xfu : colfix;
                 res = Op::select(m, L[t - 1][sc].v, res);
+            } else if (MODE == 1) {
+                res = Op::select(colfix, L[t - 1][sc].v, res);
             }
             if (t < TB) {
                 L[t < TB ? t : 0][sc] = Op::make_row(res);
@@ -378,14 +389,17 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
         const uint8_t* sp = my_smem + st * kStageBytes + lane * 16;
         const int cbase = i * kRowsPerStage;
         const int gy_base = p.row0 + ys + cbase;  // global row of this stage's first input row
-        const bool general = col_masked || (gy_base - TB < p.ylo) || (gy_base + kRowsPerStage > p.yhi) ||
-                             (cbase < 2 * TB) || (cbase + kRowsPerStage > n_in);
-        if (general)
-            stage_rows<Op, TB, true, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix, lane_valid,
-                                          lane_store, rs, rm);
+        const bool row_special = (gy_base - TB < p.ylo) || (gy_base + kRowsPerStage > p.yhi) || (cbase < 2 * TB) ||
+                                 (cbase + kRowsPerStage > n_in);
+        if (row_special)
+            stage_rows<Op, TB, 2, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix, lane_valid,
+                                       lane_store, rs, rm);
+        else if (col_masked)
+            stage_rows<Op, TB, 1, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix, lane_valid,
+                                       lane_store, rs, rm);
         else
-            stage_rows<Op, TB, false, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix,
-                                           lane_valid, lane_store, rs, rm);
+            stage_rows<Op, TB, 0, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix, lane_valid,
+                                       lane_store, rs, rm);
         __syncwarp();
         if (lane == 0 && i + kStages < n_it) issue(it + kStages, ys + (i + kStages) * kRowsPerStage);
         ++it;
@@ -411,37 +425,42 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
     }
 }
 
-// Tile order: slab-cut chunks first (their halo pushes overlap everything else), then the remaining tiles of
-// the two edge strips (fully masked = slowest, so they must not end up in the tail), then the interior.
+// Tile order within a sweep: chunks from the outside in (0, nc-1, 1, nc-2, ...), all strips of a chunk together.
+// The slab-cut chunks come first so their halo pushes overlap the rest of the sweep, and a chunk's neighbours in
+// the previous sweep were finished equally early, so the barrier-free path never has an early ticket waiting for
+// a late one.
 __device__ __forceinline__ void decode_tile(int q, int ns, int nc, int& chunk, int& strip) {
-    if (q < ns) {
-        chunk = 0;
-        strip = q;
-        return;
+    const int ci = q / ns;
+    strip = q - ci * ns;
+    chunk = (ci & 1) ? nc - 1 - (ci >> 1) : (ci >> 1);
+}
+
+// Inverse of decode_tile.
+__device__ __forceinline__ int encode_tile(int chunk, int strip, int ns, int nc) {
+    const int ci = (chunk <= nc - 1 - chunk) ? 2 * chunk : 2 * (nc - 1 - chunk) + 1;
+    return ci * ns + strip;
+}
+
+// Bounded acquire spin at GPU scope on a per-tile completion word.
+__device__ __noinline__ bool wait_tile_done(const Fused2dParams& p, const unsigned* word, unsigned need) {
+    auto ld = [&]() {
+        unsigned v;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+        return v;
+    };
+    if (ld() >= need) return true;
+    const unsigned long long t0 = ptx::globaltimer_ns();
+    unsigned spins = 0;
+    while (ld() < need) {
+        if ((++spins & 255u) == 0) {
+            if (aborted(p)) return false;
+            if (ptx::globaltimer_ns() - t0 > p.timeout_ns) {
+                atomicCAS(p.status, 0, MCP_ERR_TIMEOUT);
+                return false;
+            }
+        }
     }
-    q -= ns;
-    if (nc == 1) {  // unreachable for q < n_tiles
-        chunk = 0;
-        strip = 0;
-        return;
-    }
-    if (q < ns) {
-        chunk = nc - 1;
-        strip = q;
-        return;
-    }
-    q -= ns;
-    const int mid = nc - 2;  // interior chunks 1 .. nc-2
-    const int n_edge = ns >= 2 ? 2 : 1;
-    if (q < n_edge * mid) {
-        chunk = 1 + q / n_edge;
-        strip = (q % n_edge) ? ns - 1 : 0;
-        return;
-    }
-    q -= n_edge * mid;
-    const int inner = ns - 2;  // interior strips 1 .. ns-2 (>= 1 here)
-    chunk = 1 + q / inner;
-    strip = 1 + q % inner;
+    return true;
 }
 
 template <class Op, int TB, bool RES, int WARPS>
@@ -470,8 +489,103 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int NW = gridDim.x * WARPS;
     const int n_tiles = p.n_strips * p.n_chunks;
     uint32_t it = 0;
-    unsigned long long epoch = 0;
 
+    const bool dataflow = !RES && p.sync_mode == 2;
+    // One tile of one sweep: wait for what it reads, run it, publish what it wrote.
+    auto run_tile = [&](const int sw, const int q, double* partials) {
+        const int par = (p.first_parity + sw) & 1;
+        const CUtensorMap* tm_in = par ? &tmB : &tmA;
+        T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
+        int chunk, strip;
+        decode_tile(q, p.n_strips, p.n_chunks, chunk, strip);
+        const int y0 = __ldg(&p.chunk_y[chunk]);
+        const int y1 = __ldg(&p.chunk_y[chunk + 1]);
+        const int x_ld = strip * OUTW - M * VEC;
+        const bool top = (chunk == 0), bot = (chunk == p.n_chunks - 1);
+        T* up_out = top ? reinterpret_cast<T*>(p.up_buf[par ^ 1]) : nullptr;
+        T* dn_out = bot ? reinterpret_cast<T*>(p.dn_buf[par ^ 1]) : nullptr;
+
+        if (dataflow && sw > 0 && lane < 9) {
+            // Dataflow instead of a grid barrier: this tile reads what its (up to) 9 neighbours wrote in the
+            // previous sweep and overwrites what they read then -- both are settled once they have finished it.
+            // One lane per neighbour, so the nine acquire loads are in flight together.
+            const int c2 = chunk + lane / 3 - 1, s2 = strip + lane % 3 - 1;
+            if (c2 >= 0 && c2 < p.n_chunks && s2 >= 0 && s2 < p.n_strips)
+                wait_tile_done(p, &p.tile_done[encode_tile(c2, s2, p.n_strips, p.n_chunks)], (unsigned)sw);
+        }
+        if (lane == 0) {
+            bool ok = true;
+            // Ghost rows this tile reads were written by the neighbour GPU during its previous sweep.
+            if (up_out != nullptr)
+                ok = wait_counter_sys(p, &p.my_flags[0], p.flag_base_up + (unsigned long long)sw * p.n_strips);
+            if (ok && dn_out != nullptr)
+                ok = wait_counter_sys(p, &p.my_flags[1], p.flag_base_dn + (unsigned long long)sw * p.n_strips);
+        }
+        __syncwarp();
+        if (lane == 0) ptx::fence_proxy_async();  // generic-proxy stores (other SMs, peers) -> our TMA loads
+        __syncwarp();
+        if (aborted(p)) return;
+
+        double rs = 0.0, rm = 0.0;
+        process_tile<Op, TB, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
+
+        if (RES) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                rs += __shfl_xor_sync(0xffffffffu, rs, o);
+                rm = fmax(rm, __shfl_xor_sync(0xffffffffu, rm, o));
+            }
+            if (lane == 0) {
+                partials[2 * q] = rs;
+                partials[2 * q + 1] = rm;
+            }
+        }
+        // Publish: all lanes' stores (local rows, peer ghost rows) -> one release per consumer.
+        __syncwarp();
+        if (lane == 0) {
+            if (dataflow) {
+                ptx::fence_proxy_async();
+                __threadfence();
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&p.tile_done[q]), "r"((unsigned)(sw + 1))
+                             : "memory");
+            }
+            if (up_out != nullptr) {
+                ptx::fence_acq_rel_sys();
+                ptx::red_add_release_sys(p.up_flag, 1ull);
+            }
+            if (dn_out != nullptr) {
+                ptx::fence_acq_rel_sys();
+                ptx::red_add_release_sys(p.dn_flag, 1ull);
+            }
+        }
+    };
+
+    if (dataflow) {
+        // ---- barrier-free path: one ticket stream over all sweeps; ticket t = (sweep t / n_tiles, tile t % n_tiles).
+        // Tickets are handed out in order and a tile only ever waits for lower tickets, so the lowest unfinished
+        // ticket can always run: no deadlock as long as every CTA is resident (cooperative launch).
+        const unsigned long long total = (unsigned long long)p.sweeps * (unsigned long long)n_tiles;
+        auto grab = [&]() -> unsigned long long {
+            unsigned long long v = 0;
+            if (lane == 0) v = atomicAdd(p.tile_ctr, 1ull) - p.ctr_base;
+            return __shfl_sync(0xffffffffu, v, 0);
+        };
+        unsigned long long t = grab();
+        while (t < total) {
+            const unsigned long long t_next = grab();  // latency hidden behind this tile
+            if (!aborted(p)) {
+                const int sw = (int)(t / (unsigned long long)n_tiles);
+                const int q = (int)(t - (unsigned long long)sw * n_tiles);
+                run_tile(sw, q, nullptr);
+            }
+            t = t_next;
+        }
+        return;
+    }
+
+    // ---- barrier path: sweeps separated by a device-side grid barrier (always used with the fused residual, so
+    // that CTA 0 can reduce the per-tile partials of a finished sweep)
+    unsigned long long epoch = 0;
     int executed = 0;
     for (int sw = 0; sw < p.sweeps; ++sw) {
         if (RES && p.stop_mode != 0 && sw > 0) {
@@ -479,13 +593,6 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int s = *((volatile int*)p.stop_word);
             if (s != 0 && sw >= s) break;
         }
-        const int par = (p.first_parity + sw) & 1;
-        const CUtensorMap* tm_in = par ? &tmB : &tmA;
-        T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
-        T* up_buf_out = reinterpret_cast<T*>(p.up_buf[par ^ 1]);
-        T* dn_buf_out = reinterpret_cast<T*>(p.dn_buf[par ^ 1]);
-        const unsigned long long need_up = p.flag_base_up + (unsigned long long)sw * p.n_strips;
-        const unsigned long long need_dn = p.flag_base_dn + (unsigned long long)sw * p.n_strips;
         double* partials = p.partials + (size_t)(sw & 1) * n_tiles * 2;
 
         // Dynamic tile queue: one monotonic counter; every warp grabs until it draws a ticket past the end, so
@@ -497,80 +604,14 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             v = __shfl_sync(0xffffffffu, v, 0);
             return v < (unsigned long long)n_tiles ? (int)v : n_tiles;
         };
-
         int q = grab();
         while (q < n_tiles) {
-            const int q_next = grab();  // latency hidden behind this tile
-            if (aborted(p)) {
-                q = q_next;
-                continue;  // keep drawing tickets so the counter stays consistent
-            }
-            int chunk, strip;
-            decode_tile(q, p.n_strips, p.n_chunks, chunk, strip);
-            const int y0 = __ldg(&p.chunk_y[chunk]);
-            const int y1 = __ldg(&p.chunk_y[chunk + 1]);
-            const int x_ld = strip * OUTW - M * VEC;
-            const bool top = (chunk == 0), bot = (chunk == p.n_chunks - 1);
-            T* up_out = top ? up_buf_out : nullptr;
-            T* dn_out = bot ? dn_buf_out : nullptr;
-
-            // Ghost rows this tile reads were written by the neighbour during its previous sweep.
-            if (lane == 0) {
-                bool ok = true;
-                if (up_out != nullptr) ok = wait_counter_sys(p, &p.my_flags[0], need_up);
-                if (ok && dn_out != nullptr) ok = wait_counter_sys(p, &p.my_flags[1], need_dn);
-                ptx::fence_proxy_async();  // peer stores (generic proxy) -> our TMA loads (async proxy)
-                (void)ok;
-            }
-            __syncwarp();
-            if (aborted(p)) {
-                q = q_next;
-                continue;
-            }
-
-            double rs = 0.0, rm = 0.0;
-            process_tile<Op, TB, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
-
-            if (RES) {
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    rs += __shfl_xor_sync(0xffffffffu, rs, o);
-                    rm = fmax(rm, __shfl_xor_sync(0xffffffffu, rm, o));
-                }
-                if (lane == 0) {
-                    partials[2 * q] = rs;
-                    partials[2 * q + 1] = rm;
-                }
-            }
-            if (p.debug_flags & 1) {
-                ptx::fence_proxy_async();
-                __threadfence();
-            }
-            // Publish the halo rows this tile pushed: all lanes' peer stores -> one release per neighbour.
-            __syncwarp();
-            if (lane == 0) {
-                if (up_out != nullptr) {
-                    ptx::fence_acq_rel_sys();
-                    ptx::red_add_release_sys(p.up_flag, 1ull);
-                }
-                if (dn_out != nullptr) {
-                    ptx::fence_acq_rel_sys();
-                    ptx::red_add_release_sys(p.dn_flag, 1ull);
-                }
-            }
+            const int q_next = grab();
+            if (!aborted(p)) run_tile(sw, q, partials);
             q = q_next;
         }
 
-        const bool last = (sw + 1 == p.sweeps);
-        if (!last || RES) {
-            if (p.debug_flags & 2) {
-                cooperative_groups::this_grid().sync();
-                if (threadIdx.x == 0) ptx::red_add_release_gpu(p.grid_bar, 1ull);  // keep the counter consistent
-                ++epoch;
-            } else {
-                grid_barrier(p, epoch);
-            }
-        }
+        if (RES || sw + 1 < p.sweeps) grid_barrier(p, epoch);
         if (aborted(p)) break;
 
         if (RES && blockIdx.x == 0) {
@@ -656,6 +697,7 @@ struct mcp_fused2d_plan {
     double* res_out;
     int* chunk_tab;                 // device: kNumTb tables of kMaxChunks + 1 row boundaries
     int* stop_words;                // device: [0] stop word, [1] sweeps done
+    unsigned* tile_done;            // device: [partials_cap_tiles]
     unsigned long long res_seq;     // sweeps whose residual has been exchanged so far
     int last_generations;           // generations executed by the last run call
     std::vector<int> chunk_host[4];  // per time block 1,2,4,8
@@ -664,6 +706,7 @@ struct mcp_fused2d_plan {
     int64_t launches;
     unsigned long long timeout_ns;
     int debug_flags;
+    int sync_mode;  // 0 = choose per launch, 1 = barrier, 2 = dataflow
 };
 
 namespace {
@@ -727,7 +770,7 @@ void build_chunks(const mcp_fused2d_plan* pl, int tb, std::vector<int>* out, int
         for (int c = 1; c <= nc; ++c) y.push_back(own_lo + (int)((long long)rows * c / nc));
         return;
     }
-    const int NW = pl->grid * warps_for_tb(tb);
+    const int NW = pl->grid * warps_for(d.op == MCP_OP_LIFE, tb);
     const char* e_k = getenv("MCP_GSS_K");
     const char* e_rmin = getenv("MCP_GSS_RMIN");
     const char* e_rmax = getenv("MCP_GSS_RMAX");
@@ -766,7 +809,7 @@ void choose_geometry(const mcp_fused2d_plan* pl, int tb, int* n_strips, int* n_c
 
 template <class Op, int TB>
 int launch_variant(mcp_fused2d_plan* pl, const Fused2dParams& p, bool res, cudaStream_t stream) {
-    constexpr int W = warps_for_tb(TB);
+    constexpr int W = warps_for(std::is_same<Op, LifeI32>::value, TB);
     constexpr int smem = smem_bytes_for(W);
     void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
     const void* fn = res ? (const void*)fused2d_kernel<Op, TB, true, W> : (const void*)fused2d_kernel<Op, TB, false, W>;
@@ -833,12 +876,14 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->launches = 0;
     pl->timeout_ns = 20ull * 1000000000ull;
     pl->debug_flags = getenv("MCP_DEBUG_FLAGS") ? atoi(getenv("MCP_DEBUG_FLAGS")) : 0;
+    pl->sync_mode = getenv("MCP_SYNC_MODE") ? atoi(getenv("MCP_SYNC_MODE")) : 0;
     pl->grid_bar = nullptr;
     pl->status = nullptr;
     pl->partials = nullptr;
     pl->res_out = nullptr;
     pl->chunk_tab = nullptr;
     pl->stop_words = nullptr;
+    pl->tile_done = nullptr;
     pl->res_seq = 0;
     pl->last_generations = 0;
 
@@ -875,6 +920,11 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         mcp_fused2d_destroy(pl);
         return MCP_ERR_CUDA;
     }
+    if ((e = cudaMalloc(&pl->tile_done, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess) {
+        set_error("mcp_fused2d_create: tile flag allocation failed: %s", cudaGetErrorString(e));
+        mcp_fused2d_destroy(pl);
+        return MCP_ERR_CUDA;
+    }
     if ((e = cudaMalloc(&pl->chunk_tab, 4 * (kMaxChunks + 1) * sizeof(int))) != cudaSuccess) {
         set_error("mcp_fused2d_create: chunk table allocation failed: %s", cudaGetErrorString(e));
         mcp_fused2d_destroy(pl);
@@ -904,7 +954,7 @@ int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_stri
     if (n_strips) *n_strips = ns;
     if (n_chunks) *n_chunks = nc;
     if (grid) *grid = pl->grid;
-    if (smem_bytes) *smem_bytes = smem_bytes_for(warps_for_tb(time_block));
+    if (smem_bytes) *smem_bytes = smem_bytes_for(warps_for(pl->d.op == MCP_OP_LIFE, time_block));
     return MCP_OK;
 }
 
@@ -947,6 +997,7 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
         p.grid_bar = pl->grid_bar;
         p.tile_ctr = pl->grid_bar + 16;  // separate 128-byte line of the same zeroed allocation
         p.ctr_base = pl->ctr_base;
+        p.tile_done = pl->tile_done;
         p.status = pl->status;
         p.partials = pl->partials;
         p.res_out = pl->res_out;
@@ -985,6 +1036,16 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
         p.stop_mode = stop_mode;
         p.stop_thresh = stop_thresh;
         if (stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(pl->stop_words, 0, 2 * sizeof(int), stream));
+        // Sweep synchronisation: per-tile dataflow flags remove the barrier and the idle tail of every sweep, which
+        // pays when a warp has few tiles per sweep; with many tiles per warp the plain barrier is cheaper.
+        int sync_mode = pl->sync_mode;
+        if (sync_mode == 0) {
+            const double tiles_per_warp = (double)ns * nc / ((double)pl->grid * warps_for(d.op == MCP_OP_LIFE, tb));
+            sync_mode = (tb < 8 || tiles_per_warp < 5.0) ? 2 : 1;
+        }
+        if (res) sync_mode = 1;
+        p.sync_mode = sync_mode;
+        if (sync_mode == 2) MCP_CUDA_TRY(cudaMemsetAsync(pl->tile_done, 0, (size_t)ns * nc * sizeof(unsigned), stream));
 
         int rc = launch_any(pl, tb, p, res, stream);
         if (rc) return rc;
@@ -998,10 +1059,14 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
             executed = words[1];
             MCP_REQUIRE(executed >= 0 && executed <= sweeps, "device reported %d executed sweeps of %d", executed, sweeps);
         }
-        const unsigned long long barriers = res ? (unsigned long long)executed : (unsigned long long)(executed - 1);
-        pl->bar_base += barriers * (unsigned long long)pl->grid;
-        pl->ctr_base += (unsigned long long)executed *
-                        (unsigned long long)((long long)ns * nc + (long long)pl->grid * warps_for_tb(tb));
+        const unsigned long long nw = (unsigned long long)pl->grid * warps_for(d.op == MCP_OP_LIFE, tb);
+        if (sync_mode == 1) {
+            const unsigned long long barriers = res ? (unsigned long long)executed : (unsigned long long)(executed - 1);
+            pl->bar_base += barriers * (unsigned long long)pl->grid;
+            pl->ctr_base += (unsigned long long)executed * ((unsigned long long)ns * nc + nw);
+        } else {
+            pl->ctr_base += (unsigned long long)executed * ((unsigned long long)ns * nc) + nw;
+        }
         pl->flag_base_up += (unsigned long long)executed * ns;
         pl->flag_base_dn += (unsigned long long)executed * ns;
         pl->parity = (pl->parity + executed) & 1;
@@ -1075,6 +1140,7 @@ int mcp_fused2d_destroy(mcp_fused2d_plan* pl) {
     if (pl->res_out) cudaFree(pl->res_out);
     if (pl->chunk_tab) cudaFree(pl->chunk_tab);
     if (pl->stop_words) cudaFree(pl->stop_words);
+    if (pl->tile_done) cudaFree(pl->tile_done);
     delete pl;
     return MCP_OK;
 }
