@@ -1,4 +1,5 @@
-// Unfused residual of two fields: (sum (a-b)^2, max |a-b|) over a row range, accumulated in fp64.
+// Unfused residual of two fields: (sum (a-b)^2, max |a-b|) over a row range; a-b is formed in the field's own
+// precision (like the fused kernel), squares and sums are accumulated in fp64.
 // Two passes through a scratch array of per-block partials, combined in a fixed order, so the result is
 // bit-reproducible run to run.  The reference has no reduction of any kind (no residual, no norm, no
 // convergence test); this is the baseline for the residual fused into the sweep kernel.
@@ -19,7 +20,7 @@ __device__ __forceinline__ void block_partial(const T* __restrict__ a, const T* 
          i += (long long)gridDim.x * blockDim.x) {
         const int r = (int)(i / w), c = (int)(i - (long long)r * w);
         const long long off = (long long)(row_lo + r) * pitch + c;
-        const double d = (double)a[off] - (double)b[off];
+        const double d = (double)(T)(a[off] - b[off]);  // difference in the field's own precision
         ss = fma(d, d, ss);
         mx = fmax(mx, fabs(d));
     }

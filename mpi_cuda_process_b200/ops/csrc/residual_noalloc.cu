@@ -41,7 +41,7 @@ noalloc_row_pass(const T* __restrict__ a, const T* __restrict__ b, long long pit
     const long long base = (long long)(row_lo + r) * pitch;
     double ss = 0.0, mx = 0.0;
     for (int c = threadIdx.x; c < w; c += kRowThreads) {
-        const double d = (double)a[base + c] - (double)b[base + c];
+        const double d = (double)(T)(a[base + c] - b[base + c]);  // difference in the field's own precision
         ss = fma(d, d, ss);
         mx = fmax(mx, fabs(d));
     }

@@ -125,11 +125,18 @@ struct MdfF32 {
         o.w = (m & 8u) ? keep.w : upd.w;
         return o;
     }
+    // residual contribution of 4 cells: differences and their squares in fp32 (the field's own precision),
+    // one conversion per vector, accumulation across rows in fp64
     static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
-        const double d0 = (double)a.x - (double)b.x, d1 = (double)a.y - (double)b.y;
-        const double d2 = (double)a.z - (double)b.z, d3 = (double)a.w - (double)b.w;
-        ss = fma(d0, d0, ss); ss = fma(d1, d1, ss); ss = fma(d2, d2, ss); ss = fma(d3, d3, ss);
-        mx = fmax(mx, fmax(fmax(fabs(d0), fabs(d1)), fmax(fabs(d2), fabs(d3))));
+        const float d0 = __fsub_rn(a.x, b.x), d1 = __fsub_rn(a.y, b.y);
+        const float d2 = __fsub_rn(a.z, b.z), d3 = __fsub_rn(a.w, b.w);
+        float q = __fmul_rn(d0, d0);
+        q = __fmaf_rn(d1, d1, q);
+        q = __fmaf_rn(d2, d2, q);
+        q = __fmaf_rn(d3, d3, q);
+        ss += (double)q;
+        const float m = fmaxf(fmaxf(fabsf(d0), fabsf(d1)), fmaxf(fabsf(d2), fabsf(d3)));
+        mx = fmax(mx, (double)m);
     }
 };
 

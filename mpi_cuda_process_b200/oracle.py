@@ -96,8 +96,9 @@ def mdf_update_cells_simplified(C, N, S, W, E):
 
 
 def residual(u_new: np.ndarray, u_old: np.ndarray, kind: str = "linf") -> float:
-    """Global residual of one generation, accumulated in fp64 (deterministic on the CPU)."""
-    d = u_new.astype(np.float64) - u_old.astype(np.float64)
+    """Global residual of one generation: the difference is formed in the field's own dtype (what every kernel
+    does), its magnitude / square are reduced in fp64."""
+    d = (u_new - u_old).astype(np.float64)
     if kind == "linf":
         return float(np.max(np.abs(d))) if d.size else 0.0
     if kind == "l2":
