@@ -35,6 +35,10 @@ def parse_args(argv=None):
     p.add_argument("--steps", type=int, default=10)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="fused", choices=["fused", "ours", "reference", "nccl", "staged"])
+    p.add_argument("--workload", default="mdf", choices=["mdf", "life", "heat3d"],
+                   help="mdf = the headline config; heat3d/life for the other BASELINE.json configs")
+    p.add_argument("--depth", type=int, default=0)
+    p.add_argument("--decomposition", default="slab", choices=["slab", "pencil"])
     p.add_argument("--height", type=int, default=16384)
     p.add_argument("--width", type=int, default=16384)
     p.add_argument("--gens-per-step", type=int, default=1000)
@@ -88,7 +92,14 @@ def main(argv=None) -> int:
     h = args.height * (ctx.world if args.scaling == "weak" else 1)
     w = args.width
     gps = args.gens_per_step
-    cfg = RunConfig(workload="mdf", height=h, width=w, dtype=args.dtype, backend=backend,
+    depth = args.depth
+    if args.workload == "heat3d":
+        depth = depth or 512
+        if args.scaling == "weak" and args.decomposition == "slab":
+            depth, h = depth * ctx.world, args.height
+    cfg = RunConfig(workload=args.workload, height=h, width=w, depth=depth if args.workload == "heat3d" else 0,
+                    dtype="int32" if args.workload == "life" else args.dtype, backend=backend,
+                    decomposition=args.decomposition, seed=0 if args.workload == "life" else None,
                     time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
                     extra={"chunk_rows": args.chunk_rows})
     K, W = args.steps, max(args.warmup, 0)
@@ -117,7 +128,7 @@ def main(argv=None) -> int:
         cells = cfg.cells
         value = cells * gps * K / (ms_total * 1e-3) / 1e9
         geom = None
-        if backend == "fused":
+        if backend == "fused" and cfg.ndim == 2:
             import ctypes as C
             ns, nc, grid, smem = C.c_int(), C.c_int(), C.c_int(), C.c_int()
             s._lib.mcp_fused2d_geometry(s._plan, s.time_block, C.byref(ns), C.byref(nc), C.byref(grid), C.byref(smem))
@@ -162,16 +173,18 @@ def main(argv=None) -> int:
         if ctx.rank == 0:
             esize = 8 if args.dtype == "fp64" else 4
             cells_gpu = cells // ctx.world
-            halo = 0 if ctx.world == 1 else 2 * w * esize
+            halo = 0 if ctx.world == 1 else 2 * (cells // cfg.shape[0]) * esize
             roof = metrics.roofline(cells_gpu, gps * K, ms_total, 2 * esize, halo)
             out = {
                 "metric": METRIC, "value": round(value, 3), "unit": "GLUPS", "n_gpus": ctx.world, "steps": K,
                 "warmup": W, "ms_per_step": round(ms_total / K, 4), "higher_is_better": True,
-                "scaling": args.scaling, "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+                "scaling": args.scaling, "vs_baseline": None, "dtype": cfg.dtype, "data": "synthetic",
                 "impl": args.impl if args.impl != "ours" else "fused",
-                "config": {"model": "2-D 5-point MDF (heat/Jacobi), Dirichlet ring=100", "grid": [h, w],
+                "config": {"model": {"mdf": "2-D 5-point MDF (heat/Jacobi), Dirichlet ring=100",
+                                     "life": "Game of Life B3/S23 int32", "heat3d": "3-D 7-point heat, Dirichlet shell"}[args.workload],
+                           "grid": list(cfg.shape),
                            "global_batch": cells, "seq_len": gps, "generations_per_step": gps,
-                           "iterations": gps * K, "parallelism": f"slab{ctx.world}",
+                           "iterations": gps * K, "parallelism": f"{args.decomposition}{ctx.world}",
                            "time_block": s.time_block, "backend": s.backend,
                            "l2": "inputs larger than L2 (two %d MiB buffers per GPU stream through HBM every pass)"
                                  % (cells_gpu * esize >> 20), "geometry": geom},

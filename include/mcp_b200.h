@@ -137,6 +137,40 @@ int mcp_fused2d_geometry(const mcp_fused2d_plan* plan, int time_block, int* n_st
 int mcp_fused2d_chunks(const mcp_fused2d_plan* plan, int time_block, int* rows_out, int max_entries);
 int mcp_fused2d_destroy(mcp_fused2d_plan* plan);
 
+/* ---- fused halo + 3-D 7-point heat kernel (pencil decomposition) -------------------------------------
+ * Extension (BASELINE.json config 3); the reference is strictly 2-D (M:13-18).  One cooperative launch advances
+ * `generations` generations: TMA-fed plane ring, z-march with the three planes of a cell in registers, pencil-face
+ * cells stored straight into the four neighbour GPUs' ghost layers (z-faces: rows of a plane, y-faces: one strided
+ * row per plane) with system-scope release counters, device-side grid barrier between generations.
+ * Every rank allocates buffers of the SAME pz_alloc x py_alloc x pitch shape (sized for the largest block) so that
+ * strides agree across ranks; owned local indices are 1..nz (planes) and 1..ny (rows), ghost depth 1. */
+typedef struct mcp_fused3d_desc {
+    int dtype;            /* MCP_DTYPE_F32 or MCP_DTYPE_F64 */
+    int d, h, w;          /* global grid (planes, rows, columns) */
+    int z_start, nz;      /* first owned global plane, owned planes */
+    int y_start, ny;      /* first owned global row, owned rows */
+    int64_t pitch;        /* elements per row, multiple of 32 */
+    int py_alloc, pz_alloc;
+    void* buf[2];
+    void* nbr_buf[4][2];  /* z-, z+, y-, y+ neighbours' buffers mapped here, or NULL */
+    int nbr_n[4];         /* nz of the z-/z+ neighbours, ny of the y-/y+ neighbours */
+    uint64_t* flags;      /* local: 4 arrival counters (from z-, z+, y-, y+), zeroed */
+    uint64_t* nbr_flag[4];/* the counter of each neighbour that THIS rank bumps (its opposite-face counter) */
+    int expect[4];        /* arrivals per generation expected from each neighbour (mcp_fused3d_face_tiles) */
+    double coeff;         /* diffusion number, 1/6 = 3-D stability limit */
+    int zchunk;           /* planes per tile (0 = 32) */
+} mcp_fused3d_desc;
+typedef struct mcp_fused3d_plan mcp_fused3d_plan;
+int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out);
+/* Tiles of a block that touch its z-, z+, y-, y+ faces: what a neighbour must expect per generation. */
+int mcp_fused3d_face_tiles(int nz, int ny, int w, int dtype, int zchunk, int* counts4);
+int mcp_fused3d_run(mcp_fused3d_plan* plan, int generations, void* stream);
+int mcp_fused3d_parity(const mcp_fused3d_plan* plan);
+int mcp_fused3d_set_parity(mcp_fused3d_plan* plan, int parity);
+int mcp_fused3d_status(mcp_fused3d_plan* plan);
+int64_t mcp_fused3d_launches(const mcp_fused3d_plan* plan);
+int mcp_fused3d_destroy(mcp_fused3d_plan* plan);
+
 /* ---- residual of two fields (unfused; two-pass, fixed order, deterministic) ------------------------
  * out_host[0] = sum over the row range of (a-b)^2 in fp64, out_host[1] = max |a-b|.
  * `scratch_dev` holds at least mcp_residual2d_scratch_bytes() bytes. */

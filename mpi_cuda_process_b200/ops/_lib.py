@@ -41,6 +41,19 @@ class FusedDesc(C.Structure):
     ]
 
 
+class Fused3dDesc(C.Structure):
+    """mcp_fused3d_desc (include/mcp_b200.h)."""
+
+    _fields_ = [
+        ("dtype", C.c_int), ("d", C.c_int), ("h", C.c_int), ("w", C.c_int),
+        ("z_start", C.c_int), ("nz", C.c_int), ("y_start", C.c_int), ("ny", C.c_int),
+        ("pitch", C.c_int64), ("py_alloc", C.c_int), ("pz_alloc", C.c_int),
+        ("buf", C.c_void_p * 2), ("nbr_buf", (C.c_void_p * 2) * 4), ("nbr_n", C.c_int * 4),
+        ("flags", C.c_void_p), ("nbr_flag", C.c_void_p * 4), ("expect", C.c_int * 4),
+        ("coeff", C.c_double), ("zchunk", C.c_int),
+    ]
+
+
 def _declare_host(lib: C.CDLL) -> None:
     lib.mcp_host_life_init_reference.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float]
     lib.mcp_host_life_init_reference.restype = C.c_int
@@ -85,6 +98,15 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_geometry.argtypes = [vp, i, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i)]
     lib.mcp_fused2d_chunks.argtypes = [vp, i, vp, i]
     lib.mcp_fused2d_destroy.argtypes = [vp]
+    lib.mcp_fused3d_create.argtypes = [C.POINTER(Fused3dDesc), c_void_pp]
+    lib.mcp_fused3d_face_tiles.argtypes = [i, i, i, i, i, C.POINTER(i)]
+    lib.mcp_fused3d_run.argtypes = [vp, i, vp]
+    lib.mcp_fused3d_parity.argtypes = [vp]
+    lib.mcp_fused3d_set_parity.argtypes = [vp, i]
+    lib.mcp_fused3d_status.argtypes = [vp]
+    lib.mcp_fused3d_launches.argtypes = [vp]
+    lib.mcp_fused3d_launches.restype = i64
+    lib.mcp_fused3d_destroy.argtypes = [vp]
     lib.mcp_residual2d_scratch_bytes.restype = C.c_size_t
     lib.mcp_residual2d.argtypes = [i, vp, vp, i64, i, i, i, vp, vp, vp]
     lib.mcp_residual2d_noalloc_max_rows.restype = i

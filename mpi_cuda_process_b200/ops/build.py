@@ -28,6 +28,7 @@ CUDA_SOURCES = [
     "init_bc.cu",
     "stencil_plain.cu",
     "stencil2d_fused.cu",
+    "heat3d_fused.cu",
     "residual.cu",
     "residual_noalloc.cu",
     "gather_pack.cu",

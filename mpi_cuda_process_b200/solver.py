@@ -97,11 +97,9 @@ class Solver:
         if b == "auto":
             if not self.ctx.is_cuda:
                 return "cpu"
-            return "fused" if self.cfg.ndim == 2 else "nccl"
+            return "fused"
         if b != "cpu" and not self.ctx.is_cuda:
             raise RuntimeError(f"backend {b!r} needs a GPU")
-        if b == "fused" and self.cfg.ndim == 3:
-            raise ValueError("the fused backend covers the 2-D workloads; use backend='nccl' for heat3d")
         return b
 
     def _make_decomp(self) -> Decomposition:
@@ -124,6 +122,11 @@ class Solver:
         self.own_shape = own
         # ghost layers on every non-contiguous axis (unused at the physical boundary: stay zero)
         self.alloc_shape = tuple(n + 2 * G for n in own[:-1]) + (own[-1],)
+        if self.backend == "fused" and self.ndim == 3:
+            # the 3-D kernel stores into neighbours' buffers: every rank uses the shape of the largest block so
+            # that plane and row strides agree across ranks
+            mx = [max(b.shape[a] for b in self.decomp.blocks()) for a in range(self.ndim)]
+            self.alloc_shape = tuple(n + 2 * G for n in mx[:-1]) + (own[-1],)
         if self.ctx.is_cuda:
             from .ops import _lib
             self._lib = _lib.cuda_lib()
@@ -168,9 +171,46 @@ class Solver:
     def _stream(self) -> C.c_void_p:
         return C.c_void_p(torch.cuda.current_stream(self.ctx.device).cuda_stream)
 
+    def _ensure_plan3d(self):
+        from .ops import _lib
+        cfg = self.cfg
+        d = _lib.Fused3dDesc()
+        d.dtype = _MCP_DTYPE[cfg.dtype]
+        d.d, d.h, d.w = cfg.depth, cfg.height, cfg.width
+        d.z_start, d.nz = self.block.start[0], self.own_shape[0]
+        d.y_start, d.ny = self.block.start[1], self.own_shape[1]
+        d.pitch = self.pitch
+        d.pz_alloc, d.py_alloc = self.store_shape[0], self.store_shape[1]
+        zchunk = int(cfg.extra.get("zchunk", 0))
+        d.zchunk = zchunk
+        nbrs = [self.block.neighbors[0][0], self.block.neighbors[0][1],
+                self.block.neighbors[1][0], self.block.neighbors[1][1]]
+        opposite = [1, 0, 3, 2]
+        counts = (C.c_int * 4)()
+        for i in range(2):
+            d.buf[i] = self._buf_ptr(i)
+        for f, r in enumerate(nbrs):
+            if r is None:
+                continue
+            nb = self.decomp.block(r)
+            for i in range(2):
+                d.nbr_buf[f][i] = self._buf_ptr(i, r)
+            d.nbr_n[f] = nb.shape[0] if f < 2 else nb.shape[1]
+            d.nbr_flag[f] = self._arena.peer_ptr(r, 512 + 8 * opposite[f])
+            _lib.check(self._lib.mcp_fused3d_face_tiles(nb.shape[0], nb.shape[1], cfg.width, d.dtype, zchunk, counts))
+            d.expect[f] = counts[opposite[f]]
+        d.flags = self._arena.peer_ptr(self.ctx.rank, 512)
+        d.coeff = oracle.HEAT3D_COEFF
+        plan = C.c_void_p()
+        _lib.check(self._lib.mcp_fused3d_create(C.byref(d), C.byref(plan)), "mcp_fused3d_create")
+        self._plan = plan
+        self._desc = d
+
     def _ensure_plan(self):
         if self._plan is not None:
             return
+        if self.ndim == 3:
+            return self._ensure_plan3d()
         from .ops import _lib
         cfg, G = self.cfg, self.ghost
         d = _lib.FusedDesc()
@@ -324,7 +364,8 @@ class Solver:
     def _reset_plan_parity(self):
         if self._plan is not None:
             from .ops import _lib
-            _lib.check(self._lib.mcp_fused2d_set_parity(self._plan, self.cur))
+            setp = self._lib.mcp_fused3d_set_parity if self.ndim == 3 else self._lib.mcp_fused2d_set_parity
+            _lib.check(setp(self._plan, self.cur))
 
     # ------------------------------------------------------------------ stepping
     def run(self, generations: Optional[int] = None, residual=False, timed: bool = True) -> RunStats:
@@ -378,7 +419,25 @@ class Solver:
         return st
 
     # -- fused ---------------------------------------------------------------------------------
+    def _run_fused3d(self, g: int, residual: bool, st: RunStats) -> None:
+        from .ops import _lib
+        self._ensure_plan()
+        n = g - 1 if residual else g          # the residual needs both generations: last step separately
+        before = self._lib.mcp_fused3d_launches(self._plan)
+        if n > 0:
+            _lib.check(self._lib.mcp_fused3d_run(self._plan, n, self._stream()), "mcp_fused3d_run")
+        if residual:
+            prev = self._lib.mcp_fused3d_parity(self._plan)
+            _lib.check(self._lib.mcp_fused3d_run(self._plan, 1, self._stream()), "mcp_fused3d_run")
+            cur = self._lib.mcp_fused3d_parity(self._plan)
+            self.cur = cur
+            self._record_residual(st, self.bufs[prev], self.bufs[cur])
+        st.launches = int(self._lib.mcp_fused3d_launches(self._plan) - before)
+        self.cur = self._lib.mcp_fused3d_parity(self._plan)
+
     def _run_fused(self, g: int, residual: bool, st: RunStats) -> None:
+        if self.ndim == 3:
+            return self._run_fused3d(g, residual, st)
         from .ops import _lib
         self._ensure_plan()
         before = self._lib.mcp_fused2d_launches(self._plan)
@@ -418,7 +477,8 @@ class Solver:
         """Raise if a fused kernel recorded an error (e.g. a halo-flag wait timed out)."""
         if self._plan is not None:
             from .ops import _lib
-            _lib.check(self._lib.mcp_fused2d_status(self._plan), "fused kernel status")
+            stat = self._lib.mcp_fused3d_status if self.ndim == 3 else self._lib.mcp_fused2d_status
+            _lib.check(stat(self._plan), "fused kernel status")
 
     # -- plain kernel + exchange helpers ----------------------------------------------------------
     def _launch_plain(self, src: torch.Tensor, dst: torch.Tensor) -> None:
@@ -602,7 +662,7 @@ class Solver:
             every = max(self.time_block, every // self.time_block * self.time_block)
         total = RunStats(cells=self.cfg.cells)
         kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
-        if self.backend == "fused" and not self.cfg.extra.get("host_tolerance_loop", False):
+        if self.backend == "fused" and self.ndim == 2 and not self.cfg.extra.get("host_tolerance_loop", False):
             return self._run_to_tolerance_fused(tol, max_g, kind)
         while total.generations < max_g:
             n = min(every, max_g - total.generations)
@@ -703,7 +763,7 @@ class Solver:
         if self.ctx.is_cuda:
             torch.cuda.synchronize(self.ctx.device)
         if self._plan is not None:
-            self._lib.mcp_fused2d_destroy(self._plan)
+            (self._lib.mcp_fused3d_destroy if self.ndim == 3 else self._lib.mcp_fused2d_destroy)(self._plan)
             self._plan = None
         self.bufs = []
         if self._arena is not None:

@@ -31,6 +31,9 @@ CASES = [
     dict(workload="life", height=120, width=100, backend="nccl", g=15),
     dict(workload="heat3d", depth=40, height=36, width=70, backend="nccl", g=6),
     dict(workload="heat3d", depth=40, height=36, width=70, backend="nccl", g=6, decomposition="pencil"),
+    dict(workload="heat3d", depth=50, height=70, width=150, backend="fused", g=9),
+    dict(workload="heat3d", depth=50, height=70, width=150, backend="fused", g=9, dtype="fp64"),
+    dict(workload="heat3d", depth=43, height=77, width=260, backend="fused", g=12, decomposition="pencil"),
 ]
 
 

@@ -130,11 +130,13 @@ def test_life_full_density_edges():
         assert (s.gather() == oracle.life_run(f, g)).all()
 
 
+@pytest.mark.parametrize("backend", ["nccl", "fused"])
 @pytest.mark.parametrize("dtype", ["fp32", "fp64"])
-def test_heat3d_bitwise(dtype):
-    d, h, w, g = 21, 34, 70, 6
+@pytest.mark.parametrize("d,h,w,g", [(21, 34, 70, 6), (3, 3, 3, 2), (70, 67, 300, 5), (9, 130, 129, 7)])
+def test_heat3d_bitwise(backend, dtype, d, h, w, g):
     npdt = np.float32 if dtype == "fp32" else np.float64
-    cfg = RunConfig(workload="heat3d", depth=d, height=h, width=w, backend="nccl", dtype=dtype)
+    cfg = RunConfig(workload="heat3d", depth=d, height=h, width=w, backend=backend, dtype=dtype,
+                    extra={"zchunk": 16})
     with Solver(cfg) as s:
         s.initialize()
         s.run(g)
@@ -283,3 +285,19 @@ def test_fused_run_to_tolerance_single_launch():
         # the solver can keep going afterwards (counters stayed consistent)
         s.run(8)
         assert s.gather().tobytes() == oracle.mdf_run(oracle.mdf_init(h, w), st.generations + 8).tobytes()
+
+
+def test_heat3d_fused_random_field_and_residual():
+    d, h, w, g = 40, 70, 200, 6
+    rng = np.random.default_rng(5)
+    f = oracle.heat3d_init(d, h, w)
+    f[1:-1, 1:-1, 1:-1] = rng.uniform(0, 100, (d - 2, h - 2, w - 2)).astype(np.float32)
+    cfg = RunConfig(workload="heat3d", depth=d, height=h, width=w, backend="fused", residual="linf")
+    with Solver(cfg) as s:
+        s.initialize(f)
+        st = s.run(g, residual=True)
+        s.check_status()
+        ref_prev = oracle.heat3d_run(f, g - 1)
+        ref = oracle.heat3d_step(ref_prev)
+        assert s.gather().tobytes() == ref.tobytes()
+        assert st.residual_history[-1][1] == oracle.residual(ref, ref_prev, "linf")
