@@ -204,6 +204,12 @@ int mcp_residual2d_noalloc(int dtype, const void* a_dev, const void* b_dev, int6
 int mcp_pack_rows(int dtype, int mode, const void* src_dev, int64_t pitch, int w, int row_lo, int row_hi,
                   void* dst_dev, int64_t dst_row0, void* stream);
 
+/* Same for a 3-D block (pencils): owned planes [z_lo, z_lo+nz) x rows [y_lo, y_lo+ny) x [0,w) of a
+ * (planes, rows, pitch) buffer into a dense (D, dst_h, w) destination at plane dst_z0, row dst_y0.
+ * mode 0 = raw copy, 1 = fp64 -> fp32.  A 2-D slab is the case nz = 1. */
+int mcp_pack_block(int dtype, int mode, const void* src_dev, int64_t pitch, int64_t plane_pitch, int z_lo, int nz,
+                   int y_lo, int ny, int w, void* dst_dev, int64_t dst_h, int64_t dst_z0, int64_t dst_y0, void* stream);
+
 /* ---- CPU reference (host code; works without a GPU) ------------------------------------------------ */
 /* glibc rand() stream exactly as the reference consumes it (K:141-142): fills an h x w int32 grid. */
 int mcp_host_life_init_reference(int32_t* u, int h, int w, float prob);

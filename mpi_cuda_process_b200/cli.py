@@ -130,10 +130,15 @@ def main(argv: Optional[List[str]] = None) -> int:
         else:
             stats = solver.run(g, residual=cfg.residual != "none")
         solver.check_status()
-        need_field = bool(args.output or args.print_field or args.check)
+        need_field = bool(args.output or args.check or (args.print_field and cfg.workload != "life"))
         field = solver.gather() if need_field else None
+        ascii_bytes = solver.gather_ascii() if (args.print_field and cfg.workload == "life") else None
         if ctx.rank == 0:
-            if args.print_field and field is not None:
+            if ascii_bytes is not None:
+                sys.stdout.flush()
+                sys.stdout.buffer.write(ascii_bytes)
+                sys.stdout.buffer.flush()
+            elif args.print_field and field is not None:
                 mio.print_array(field)
             if args.output and field is not None:
                 mio.dump_field(field, args.output, cfg.output_format)

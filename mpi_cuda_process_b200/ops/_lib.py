@@ -112,6 +112,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_residual2d_noalloc_max_rows.restype = i
     lib.mcp_residual2d_noalloc.argtypes = [i, vp, vp, i64, i, i, i, vp, vp]
     lib.mcp_pack_rows.argtypes = [i, i, vp, i64, i, i, i, vp, i64, vp]
+    lib.mcp_pack_block.argtypes = [i, i, vp, i64, i64, i, i, i, i, i, vp, i64, i64, i64, vp]
 
 
 def host_lib() -> C.CDLL:

@@ -31,9 +31,53 @@ __global__ void pack_ascii_kernel(const int* __restrict__ src, long long pitch, 
     }
 }
 
+// Block version for pencils: owned planes/rows of a (planes, rows, pitch) buffer -> dense (D, H, W) destination.
+template <class TS, class TD>
+__global__ void pack_block_kernel(const TS* __restrict__ src, long long pitch, long long plane_pitch, int z_lo, int nz,
+                                  int y_lo, int ny, int w, TD* __restrict__ dst, long long H, long long dst_z0,
+                                  long long dst_y0) {
+    const long long n = (long long)nz * ny * w;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % w);
+        const long long t = i / w;
+        const int y = (int)(t % ny), z = (int)(t / ny);
+        dst[((dst_z0 + z) * H + (dst_y0 + y)) * w + c] =
+            (TD)src[(long long)(z_lo + z) * plane_pitch + (long long)(y_lo + y) * pitch + c];
+    }
+}
+
 }  // namespace mcp
 
 using namespace mcp;
+
+extern "C" int mcp_pack_block(int dtype, int mode, const void* src, int64_t pitch, int64_t plane_pitch, int z_lo, int nz,
+                              int y_lo, int ny, int w, void* dst, int64_t dst_h, int64_t dst_z0, int64_t dst_y0,
+                              void* stream) {
+    MCP_REQUIRE(src && dst && nz >= 0 && ny >= 0 && w >= 1, "mcp_pack_block: bad arguments");
+    if (nz == 0 || ny == 0) return MCP_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long n = (long long)nz * ny * w;
+    const int grid = (int)std::min<long long>(148 * 8, (n + 255) / 256);
+    if (mode == 0 && dtype == MCP_DTYPE_F32)
+        pack_block_kernel<float, float><<<grid, 256, 0, s>>>((const float*)src, pitch, plane_pitch, z_lo, nz, y_lo, ny, w,
+                                                             (float*)dst, dst_h, dst_z0, dst_y0);
+    else if (mode == 0 && dtype == MCP_DTYPE_F64)
+        pack_block_kernel<double, double><<<grid, 256, 0, s>>>((const double*)src, pitch, plane_pitch, z_lo, nz, y_lo, ny,
+                                                               w, (double*)dst, dst_h, dst_z0, dst_y0);
+    else if (mode == 0 && dtype == MCP_DTYPE_I32)
+        pack_block_kernel<int, int><<<grid, 256, 0, s>>>((const int*)src, pitch, plane_pitch, z_lo, nz, y_lo, ny, w,
+                                                         (int*)dst, dst_h, dst_z0, dst_y0);
+    else if (mode == 1 && dtype == MCP_DTYPE_F64)
+        pack_block_kernel<double, float><<<grid, 256, 0, s>>>((const double*)src, pitch, plane_pitch, z_lo, nz, y_lo, ny,
+                                                              w, (float*)dst, dst_h, dst_z0, dst_y0);
+    else {
+        set_error("mcp_pack_block: unsupported mode %d for dtype %d", mode, dtype);
+        return MCP_ERR_UNSUPPORTED;
+    }
+    MCP_CUDA_TRY(cudaGetLastError());
+    return MCP_OK;
+}
 
 extern "C" int mcp_pack_rows(int dtype, int mode, const void* src, int64_t pitch, int w, int row_lo, int row_hi,
                              void* dst, int64_t dst_row0, void* stream) {

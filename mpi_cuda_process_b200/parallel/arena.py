@@ -99,3 +99,49 @@ class SymmetricArena:
                 self.close()
         except Exception:
             pass
+
+
+class SharedBuffer:
+    """A device buffer owned by ONE rank and mapped into every other rank (CUDA IPC): the destination of the fused
+    gather + pack, where every rank's pack kernel stores its block straight into rank 0's output over NVLink.
+    The reference has no gather at all (every rank keeps a replica of the whole grid, MDF_kernel.cu:137-144)."""
+
+    def __init__(self, ctx, nbytes: int, owner: int = 0):
+        self.ctx, self.nbytes, self.owner = ctx, int(nbytes), owner
+        self.lib = _lib.cuda_lib()
+        self.ptr = 0
+        self._mapped = False
+        hsz = self.lib.mcp_ipc_handle_size()
+        handle = None
+        if ctx.rank == owner:
+            base = C.c_void_p()
+            _lib.check(self.lib.mcp_arena_alloc(self.nbytes, C.byref(base)), "mcp_arena_alloc")
+            self.ptr = int(base.value)
+            if ctx.distributed:
+                hbuf = (C.c_ubyte * hsz)()
+                _lib.check(self.lib.mcp_ipc_get_handle(base, hbuf), "mcp_ipc_get_handle")
+                handle = bytes(hbuf)
+        if ctx.distributed:
+            handle = ctx.broadcast_object(handle, owner)
+            if ctx.rank != owner:
+                hb = (C.c_ubyte * hsz).from_buffer_copy(handle)
+                p = C.c_void_p()
+                _lib.check(self.lib.mcp_ipc_open_handle(hb, C.byref(p)), "mcp_ipc_open_handle")
+                self.ptr = int(p.value)
+                self._mapped = True
+            ctx.barrier()
+
+    def view(self, shape, dtype: torch.dtype) -> torch.Tensor:
+        assert self.ctx.rank == self.owner
+        return tensor_from_ptr(self.ptr, shape, dtype, self.ctx.device, owner=self)
+
+    def close(self) -> None:
+        if not self.ptr:
+            return
+        if self.ctx.distributed:
+            self.ctx.barrier()
+        if self._mapped:
+            self.lib.mcp_ipc_close_handle(C.c_void_p(self.ptr))
+        elif self.ctx.rank == self.owner:
+            self.lib.mcp_arena_free(C.c_void_p(self.ptr))
+        self.ptr = 0

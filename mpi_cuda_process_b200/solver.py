@@ -737,12 +737,16 @@ class Solver:
         sl = tuple(slice(G, G + n) for n in self.own_shape[:-1]) + (slice(0, self.cfg.width),)
         return self.bufs[self.cur][sl]
 
-    def gather(self) -> Optional[np.ndarray]:
-        """Assemble the global field on rank 0 (None elsewhere).  The reference has no gather: every rank holds
-        (a stale copy of) the whole grid (MDF_kernel.cu:137-144)."""
-        loc = self.local_owned()
+    def gather(self, as_fp32: bool = False) -> Optional[np.ndarray]:
+        """Assemble the global field on rank 0 (None elsewhere).
+
+        On GPUs this is the fused gather + pack: every rank's pack kernel strips ghosts and pad (and optionally
+        casts fp64 -> fp32) while storing its block straight into rank 0's output buffer over NVLink; no
+        intermediate copies, no NCCL.  The reference has no gather: every rank holds (a stale copy of) the whole
+        grid (MDF_kernel.cu:137-144)."""
         if self.ctx.is_cuda:
-            torch.cuda.synchronize(self.ctx.device)
+            return self._gather_p2p(as_fp32)
+        loc = self.local_owned()
         arr = loc.detach().cpu().contiguous().numpy()
         if not self.ctx.distributed:
             return arr.copy()
@@ -753,6 +757,65 @@ class Solver:
         for start, a in parts:
             sl = tuple(slice(s, s + n) for s, n in zip(start, a.shape))
             out[sl] = a
+        return out
+
+    def _gather_p2p(self, as_fp32: bool) -> Optional[np.ndarray]:
+        from .ops import _lib
+        from .parallel.arena import SharedBuffer
+        cfg, G = self.cfg, self.ghost
+        cast = as_fp32 and cfg.dtype == "fp64"
+        out_t = torch.float32 if cast else self.tdtype
+        out_np = np.float32 if cast else self.npdtype
+        esz = 4 if (cast or cfg.dtype != "fp64") else 8
+        key = (esz,)
+        if getattr(self, "_gather_buf", None) is None or self._gather_key != key:
+            if getattr(self, "_gather_buf", None) is not None:
+                self._gather_buf.close()
+            self._gather_buf = SharedBuffer(self.ctx, cfg.cells * esz, owner=0)
+            self._gather_key = key
+        shape3 = cfg.shape if self.ndim == 3 else (1,) + tuple(cfg.shape)
+        if self.ndim == 3:
+            z_lo, nz, y_lo, ny = G, self.own_shape[0], G, self.own_shape[1]
+            plane_pitch = self.store_shape[1] * self.pitch
+            dz0, dy0 = self.block.start[0], self.block.start[1]
+        else:
+            z_lo, nz, y_lo, ny = 0, 1, G, self.own_shape[0]
+            plane_pitch = self.store_shape[0] * self.pitch
+            dz0, dy0 = 0, self.block.start[0]
+        self.ctx.barrier()          # rank 0's previous reader is done with the buffer
+        _lib.check(self._lib.mcp_pack_block(_MCP_DTYPE[cfg.dtype], 1 if cast else 0, self.bufs[self.cur].data_ptr(),
+                                            self.pitch, plane_pitch, z_lo, nz, y_lo, ny, cfg.width,
+                                            self._gather_buf.ptr, shape3[1], dz0, dy0, self._stream()), "mcp_pack_block")
+        torch.cuda.synchronize(self.ctx.device)
+        self.ctx.barrier()          # every rank's stores have landed in rank 0's memory
+        if self.ctx.rank != 0:
+            return None
+        return self._gather_buf.view(cfg.shape, out_t).cpu().numpy().astype(out_np, copy=False)
+
+    def gather_ascii(self) -> Optional[bytes]:
+        """Life grids: the bytes the reference's ``print_array`` would print (kernel.cu:115-129), produced on the
+        GPUs -- every rank packs its rows to '0' / ' ' / newline bytes straight into rank 0's buffer."""
+        if self.cfg.workload != "life":
+            raise ValueError("print_array takes int grids only (it cannot print the float field, SURVEY D16)")
+        if not self.ctx.is_cuda:
+            from . import io as mio
+            f = self.gather()
+            return mio.format_array(f) if f is not None else None
+        from .ops import _lib
+        from .parallel.arena import SharedBuffer
+        h, w, G = self.cfg.height, self.cfg.width, self.ghost
+        buf = SharedBuffer(self.ctx, h * (w + 1), owner=0)
+        try:
+            _lib.check(self._lib.mcp_pack_rows(2, 2, self.bufs[self.cur].data_ptr(), self.pitch, w, G,
+                                               G + self.own_shape[0], buf.ptr, self.block.start[0], self._stream()),
+                       "mcp_pack_rows")
+            torch.cuda.synchronize(self.ctx.device)
+            self.ctx.barrier()
+            out = None
+            if self.ctx.rank == 0:
+                out = b"\n" + buf.view((h * (w + 1),), torch.uint8).cpu().numpy().tobytes() + b"\n"
+        finally:
+            buf.close()
         return out
 
     # ------------------------------------------------------------------ teardown
@@ -766,6 +829,9 @@ class Solver:
             (self._lib.mcp_fused3d_destroy if self.ndim == 3 else self._lib.mcp_fused2d_destroy)(self._plan)
             self._plan = None
         self.bufs = []
+        if getattr(self, "_gather_buf", None) is not None:
+            self._gather_buf.close()
+            self._gather_buf = None
         if self._arena is not None:
             self._arena.close()
             self._arena = None

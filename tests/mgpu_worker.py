@@ -111,6 +111,19 @@ def main() -> int:
             ok = ctx.broadcast_object(ok, 0)
             if not ok:
                 rc = 1
+    # fused gather + pack over NVLink: print_array bytes assembled on rank 0 by all ranks' pack kernels
+    if rc == 0:
+        from mpi_cuda_process_b200 import io as mio
+        cfg = RunConfig(workload="life", height=97, width=61, backend="fused", time_block=2)
+        with Solver(cfg, ctx=ctx) as s:
+            s.initialize()
+            s.run(7)
+            got = s.gather_ascii()
+            if ctx.rank == 0:
+                ok = got == mio.format_array(oracle.life_run(oracle.life_init_reference(97, 61), 7))
+                print(json.dumps({"case": "gather_ascii p2p", "world": ctx.world, "ok": bool(ok)}), flush=True)
+                rc = 0 if ok else 1
+        rc = ctx.broadcast_object(rc, 0)
     ctx.close()
     return rc
 

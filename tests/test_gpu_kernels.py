@@ -301,3 +301,20 @@ def test_heat3d_fused_random_field_and_residual():
         ref = oracle.heat3d_step(ref_prev)
         assert s.gather().tobytes() == ref.tobytes()
         assert st.residual_history[-1][1] == oracle.residual(ref, ref_prev, "linf")
+
+
+def test_gather_ascii_and_fp32_cast_on_device():
+    from mpi_cuda_process_b200 import io as mio
+    cfg = RunConfig(workload="life", height=33, width=47, backend="fused", time_block=2)
+    with Solver(cfg) as s:
+        s.initialize()
+        s.run(5)
+        ref = oracle.life_run(oracle.life_init_reference(33, 47), 5)
+        assert s.gather_ascii() == mio.format_array(ref)
+    cfg = RunConfig(workload="mdf", height=40, width=50, backend="fused", dtype="fp64")
+    with Solver(cfg) as s:
+        s.initialize()
+        s.run(9)
+        ref = oracle.mdf_run(oracle.mdf_init(40, 50, dtype=np.float64), 9)
+        got = s.gather(as_fp32=True)
+        assert got.dtype == np.float32 and got.tobytes() == ref.astype(np.float32).tobytes()
