@@ -56,6 +56,10 @@ int mcp_enable_peer_access(int peer_device);
  * row r is row0 + r; cells outside the h x w domain (ghost rows of edge ranks, pad columns) are 0. */
 int mcp_init_ring2d(int dtype, void* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double ring,
                     double interior, void* stream);
+/* Synthetic MDF fields (exactly reproducible on the host): kind 1 = interior uniform in [interior, ring) from
+ * hash32(i*w+j, seed); kind 2 = hot box (value ring) over the central third.  The Dirichlet ring stays at `ring`. */
+int mcp_init_shape2d(int dtype, int kind, void* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w,
+                     double ring, double interior, uint32_t seed, void* stream);
 /* Seeded synthetic life field: ring dead, interior alive iff hash32(i*w+j, seed) < prob * 2^32. */
 int mcp_init_life_hash(int32_t* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double prob,
                        uint32_t seed, void* stream);

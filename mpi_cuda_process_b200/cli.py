@@ -59,6 +59,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--residual", choices=["none", "l2", "linf"], default="none")
     p.add_argument("--seed", type=int, default=None)
     p.add_argument("--prob", type=float, default=0.15)
+    p.add_argument("--init", choices=["ring", "hash", "box"], default="ring", help="mdf initial field")
     p.add_argument("--ring", type=float, default=100.0)
     p.add_argument("--interior", type=float, default=0.0)
     p.add_argument("--halo-message", choices=["row", "element"], default="row")
@@ -99,7 +100,7 @@ def main(argv: Optional[List[str]] = None) -> int:
         workload=args.workload, generations=g, height=h, width=w, depth=args.depth,
         dtype="int32" if args.workload == "life" else args.dtype,
         bc=args.bc,
-        ring=args.ring, interior=args.interior, prob=args.prob, seed=args.seed, backend=args.backend,
+        ring=args.ring, interior=args.interior, prob=args.prob, init=args.init, seed=args.seed, backend=args.backend,
         decomposition=args.decomposition, pencil=tuple(args.pencil), time_block=args.time_block, tol=args.tol,
         max_generations=args.max_generations, residual=args.residual, halo_message=args.halo_message,
         output=args.output, output_format=args.output_format or ("ascii" if args.workload == "life" else "npy"),

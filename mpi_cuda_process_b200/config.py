@@ -59,6 +59,7 @@ class RunConfig:
     ring: float = 100.0
     interior: float = 0.0
     prob: float = 0.15
+    init: str = "ring"                   # mdf: ring (reference) | hash (random interior) | box (hot box)
     seed: Optional[int] = None
     backend: str = "auto"
     decomposition: str = "slab"          # "slab" (1-D rows) or "pencil" (2-D over a 3-D grid)
@@ -108,6 +109,8 @@ class RunConfig:
             raise ValueError("residual must be none|l2|linf")
         if self.tol is not None and self.residual == "none":
             self.residual = "linf"
+        if self.init not in ("ring", "hash", "box"):
+            raise ValueError("init must be ring|hash|box")
         if self.halo_message not in ("row", "element"):
             raise ValueError("halo_message must be row|element")
 

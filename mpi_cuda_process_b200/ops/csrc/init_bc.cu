@@ -47,6 +47,33 @@ __global__ void init_life_hash_kernel(int* __restrict__ u, long long pitch, int 
     }
 }
 
+// Synthetic initial fields beyond the reference's ring (all exactly reproducible on the host, oracle.py):
+// kind 1: interior cells uniform in [interior, ring) from hash32(i*w+j, seed) (24 random bits);
+// kind 2: a hot box (value ring) over the central third of the domain, interior elsewhere.  Ring = ring either way.
+template <class T>
+__global__ void init_shape2d_kernel(T* __restrict__ u, long long pitch, int rows_alloc, int row0, int h, int w,
+                                    double ring, double interior, int kind, unsigned seed) {
+    const long long n = (long long)rows_alloc * pitch;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(i / pitch), c = (int)(i - (long long)r * pitch);
+        const int gy = row0 + r;
+        double v = 0.0;
+        if (gy >= 0 && gy < h && c < w) {
+            if (gy == 0 || gy == h - 1 || c == 0 || c == w - 1) {
+                v = ring;
+            } else if (kind == 1) {
+                const unsigned hsh = hash32((unsigned)((long long)gy * w + c), seed);
+                v = interior + (ring - interior) * ((double)(hsh >> 8) * (1.0 / 16777216.0));
+            } else {
+                const bool hot = gy >= h / 3 && gy < h - h / 3 && c >= w / 3 && c < w - w / 3;
+                v = hot ? ring : interior;
+            }
+        }
+        u[i] = (T)v;
+    }
+}
+
 template <class T>
 __global__ void apply_ring2d_kernel(T* __restrict__ u, long long pitch, int rows_alloc, int row0, int h, int w,
                                     T ring) {
@@ -111,6 +138,24 @@ int mcp_init_ring2d(int dtype, void* u, int64_t pitch, int rows_alloc, int row0,
                                                             (int)interior);
     else
         MCP_REQUIRE(false, "bad dtype %d", dtype);
+    MCP_CUDA_TRY(cudaGetLastError());
+    return MCP_OK;
+}
+
+int mcp_init_shape2d(int dtype, int kind, void* u, int64_t pitch, int rows_alloc, int row0, int h, int w, double ring,
+                     double interior, uint32_t seed, void* stream) {
+    MCP_REQUIRE(u && pitch >= w && rows_alloc > 0, "mcp_init_shape2d: bad arguments");
+    MCP_REQUIRE(kind == 1 || kind == 2, "mcp_init_shape2d: kind must be 1 (hash) or 2 (box)");
+    const long long n = (long long)rows_alloc * pitch;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == MCP_DTYPE_F32)
+        init_shape2d_kernel<float><<<grid_for(n), 256, 0, s>>>((float*)u, pitch, rows_alloc, row0, h, w, ring, interior,
+                                                               kind, seed);
+    else if (dtype == MCP_DTYPE_F64)
+        init_shape2d_kernel<double><<<grid_for(n), 256, 0, s>>>((double*)u, pitch, rows_alloc, row0, h, w, ring,
+                                                                interior, kind, seed);
+    else
+        MCP_REQUIRE(false, "mcp_init_shape2d: bad dtype %d", dtype);
     MCP_CUDA_TRY(cudaGetLastError());
     return MCP_OK;
 }

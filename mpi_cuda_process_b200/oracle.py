@@ -30,6 +30,28 @@ def mdf_init(h: int, w: int, ring: float = 100.0, interior: float = 0.0, dtype=n
     return u
 
 
+def mdf_init_shape(h: int, w: int, kind: str, ring: float = 100.0, interior: float = 0.0, seed: int = 0,
+                   dtype=np.float32) -> np.ndarray:
+    """Synthetic MDF fields (extension): "hash" = interior uniform in [interior, ring) from hash_u32(i*w+j, seed)
+    (24 bits), "box" = hot box over the central third.  Evaluated in fp64 and cast, exactly like the device kernel."""
+    if kind == "ring":
+        return mdf_init(h, w, ring, interior, dtype)
+    if kind == "hash":
+        idx = (np.arange(h, dtype=np.int64)[:, None] * w + np.arange(w, dtype=np.int64)[None, :])
+        hsh = hash_u32(idx.astype(np.uint32), seed)
+        v = interior + (ring - interior) * ((hsh >> np.uint32(8)).astype(np.float64) * (1.0 / 16777216.0))
+    elif kind == "box":
+        v = np.full((h, w), float(interior))
+        v[h // 3:h - h // 3, w // 3:w - w // 3] = ring
+    else:
+        raise ValueError(f"unknown init {kind!r}")
+    v[0, :] = ring
+    v[-1, :] = ring
+    v[:, 0] = ring
+    v[:, -1] = ring
+    return v.astype(dtype)
+
+
 def mdf_update_cells(C, N, S, W, E):
     """The pinned rounding sequence of MDF_kernel.cu:20 for arrays of one float dtype.
 
@@ -279,7 +301,7 @@ def init_field(cfg) -> np.ndarray:
     """Global initial field for a RunConfig (single-domain)."""
     if cfg.workload == "mdf":
         dt = np.float32 if cfg.dtype == "fp32" else np.float64
-        return mdf_init(cfg.height, cfg.width, cfg.ring, cfg.interior, dt)
+        return mdf_init_shape(cfg.height, cfg.width, cfg.init, cfg.ring, cfg.interior, cfg.seed or 0, dt)
     if cfg.workload == "life":
         if cfg.seed is None:
             return life_init_reference(cfg.height, cfg.width, cfg.prob)

@@ -278,6 +278,11 @@ class Solver:
                 if cfg.workload == "life":
                     _lib.check(self._lib.mcp_init_life_hash(b.data_ptr(), self.pitch, self.store_shape[0], row0,
                                                             cfg.height, cfg.width, cfg.prob, cfg.seed, s))
+                elif cfg.workload == "mdf" and cfg.init != "ring":
+                    _lib.check(self._lib.mcp_init_shape2d(_MCP_DTYPE[cfg.dtype], 1 if cfg.init == "hash" else 2,
+                                                          b.data_ptr(), self.pitch, self.store_shape[0], row0,
+                                                          cfg.height, cfg.width, cfg.ring, cfg.interior,
+                                                          cfg.seed or 0, s))
                 else:
                     _lib.check(self._lib.mcp_init_ring2d(_MCP_DTYPE[cfg.dtype], b.data_ptr(), self.pitch,
                                                          self.store_shape[0], row0, cfg.height, cfg.width,
@@ -396,6 +401,8 @@ class Solver:
                 ev0.record()
         else:
             t0 = time.perf_counter()
+        if self.ctx.is_cuda:
+            torch.cuda.nvtx.range_push(f"mcp.run[{self.backend}] {self.cfg.workload} g={g}")
         if self.backend == "fused":
             self._run_fused(g, residual, st)
         elif self.backend == "nccl":
@@ -405,6 +412,7 @@ class Solver:
         else:
             self._run_cpu(g, residual, st)
         if self.ctx.is_cuda:
+            torch.cuda.nvtx.range_pop()
             if timed:
                 ev1.record()
                 ev1.synchronize()

@@ -318,3 +318,16 @@ def test_gather_ascii_and_fp32_cast_on_device():
         ref = oracle.mdf_run(oracle.mdf_init(40, 50, dtype=np.float64), 9)
         got = s.gather(as_fp32=True)
         assert got.dtype == np.float32 and got.tobytes() == ref.astype(np.float32).tobytes()
+
+
+@pytest.mark.parametrize("init", ["hash", "box"])
+@pytest.mark.parametrize("dtype", ["fp32", "fp64"])
+def test_device_init_shapes_and_run(init, dtype):
+    npdt = np.float32 if dtype == "fp32" else np.float64
+    cfg = RunConfig(workload="mdf", height=150, width=203, backend="fused", init=init, seed=3, dtype=dtype, time_block=4)
+    with Solver(cfg) as s:
+        s.initialize()
+        f0 = oracle.mdf_init_shape(150, 203, init, seed=3, dtype=npdt)
+        assert s.gather().tobytes() == f0.tobytes()
+        s.run(13)
+        assert s.gather().tobytes() == oracle.mdf_run(f0, 13).tobytes()
