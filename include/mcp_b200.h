@@ -162,7 +162,7 @@ typedef struct mcp_fused3d_desc {
     uint64_t* nbr_flag[4];/* the counter of each neighbour that THIS rank bumps (its opposite-face counter) */
     int expect[4];        /* arrivals per generation expected from each neighbour (mcp_fused3d_face_tiles) */
     double coeff;         /* diffusion number, 1/6 = 3-D stability limit */
-    int zchunk;           /* planes per tile (0 = 32) */
+    int zchunk;           /* planes per tile (0 = 64) */
 } mcp_fused3d_desc;
 typedef struct mcp_fused3d_plan mcp_fused3d_plan;
 int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out);

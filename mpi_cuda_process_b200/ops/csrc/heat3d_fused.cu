@@ -16,6 +16,7 @@
 // Arithmetic: oracle.heat3d_update_cells, every operation individually rounded.
 #include <algorithm>
 #include <new>
+#include <type_traits>
 #include <vector>
 
 #include "../../../include/mcp_b200.h"
@@ -201,6 +202,10 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             ptx::mbar_wait(&bars[(use + 1) % k3Slots], ((use + 1) / k3Slots) & 1u);
             load6(use + 1, Cc);
 
+            // GEN = the tile touches a pencil face (halo pushes) or holds fixed cells (masks); interior tiles
+            // run the lean instantiation: no masks, no push tests, unconditional stores.
+            auto zloop = [&](auto gen_tag) {
+            constexpr bool GEN = decltype(gen_tag)::value;
             for (int s = 0; s < zhi - zlo; ++s) {
                 const int pz = zlo + s;                // plane being computed
                 const uint32_t uC = use + 1 + s, uD = use + 2 + s;
@@ -220,31 +225,31 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const T* pd = reinterpret_cast<const T*>(&Dn[i + 1]);
                     V o;
                     T* po = reinterpret_cast<T*>(&o);
-                    const bool rfix = zfix || ((yfix >> i) & 1u);
+                    const bool rfix = GEN && (zfix || ((yfix >> i) & 1u));
 #pragma unroll
                     for (int k = 0; k < VEC; ++k) {
                         const T W = k == 0 ? wl : pc[k - 1];
                         const T E = k == VEC - 1 ? er : pc[k + 1];
                         const T v = heat3d_cell(pc[k], pn[k], ps[k], W, E, pu[k], pd[k], coeff);
-                        po[k] = (rfix || ((xfix >> k) & 1u)) ? pc[k] : v;
+                        po[k] = (GEN && (rfix || ((xfix >> k) & 1u))) ? pc[k] : v;
                     }
-                    if ((ystore >> i) & 1u) {
+                    if (!GEN || ((ystore >> i) & 1u)) {
                         const int ly = ylo + r0 + i;
                         uint4 bits;
                         memcpy(&bits, &o, 16);
                         const long long off = (long long)ly * p.pitch + cx;
                         ptx::st_global_v4(out + (long long)pz * p.plane_pitch + off, bits);
                         // halo pushes: z-faces are whole rows of the first/last owned plane, y-faces one row per plane
-                        if (pz == 1 && p.nbr_buf[0][0] != nullptr)
+                        if (GEN && pz == 1 && p.nbr_buf[0][0] != nullptr)
                             ptx::st_global_v4(reinterpret_cast<T*>(p.nbr_buf[0][par ^ 1]) +
                                                   (long long)(p.nbr_n[0] + 1) * p.plane_pitch + off, bits);
-                        if (pz == p.nz && p.nbr_buf[1][0] != nullptr)
+                        if (GEN && pz == p.nz && p.nbr_buf[1][0] != nullptr)
                             ptx::st_global_v4(reinterpret_cast<T*>(p.nbr_buf[1][par ^ 1]) + off, bits);
-                        if (ly == 1 && p.nbr_buf[2][0] != nullptr)
+                        if (GEN && ly == 1 && p.nbr_buf[2][0] != nullptr)
                             ptx::st_global_v4(reinterpret_cast<T*>(p.nbr_buf[2][par ^ 1]) +
                                                   (long long)pz * p.plane_pitch +
                                                   (long long)(p.nbr_n[2] + 1) * p.pitch + cx, bits);
-                        if (ly == p.ny && p.nbr_buf[3][0] != nullptr)
+                        if (GEN && ly == p.ny && p.nbr_buf[3][0] != nullptr)
                             ptx::st_global_v4(reinterpret_cast<T*>(p.nbr_buf[3][par ^ 1]) +
                                                   (long long)pz * p.plane_pitch + cx, bits);
                     }
@@ -256,6 +261,11 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 __syncthreads();  // slot of plane pz-1 (use + s) is free: nobody reads it any more
                 if (tid == 0 && s + k3Slots < n_planes) issue(use + s + k3Slots, zlo - 1 + s + k3Slots);
             }
+            };
+            const bool lean = !f_zm && !f_zp && !f_ym && !f_yp && (p.z0 + zlo >= 1) && (p.z0 + zhi - 1 <= p.d - 2) &&
+                              (p.y0 + ylo >= 1) && (p.y0 + ylo + k3TileRows - 1 <= p.h - 2) && (x0 >= 1) &&
+                              (x0 + XS - 1 <= p.w - 2);
+            if (lean) zloop(std::false_type{}); else zloop(std::true_type{});
             use += n_planes;
 
             // publish the pushed halo layers: all threads' peer stores -> one release per face
@@ -342,7 +352,7 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
     int rc = device_sm_count(&sm);
     if (rc) { delete pl; return rc; }
     pl->grid = 2 * sm;
-    pl->zchunk = d.zchunk > 0 ? d.zchunk : 32;
+    pl->zchunk = d.zchunk > 0 ? d.zchunk : 64;
 
     const int esz = d.dtype == MCP_DTYPE_F64 ? 8 : 4;
     for (int b = 0; b < 2; ++b) {
@@ -381,7 +391,7 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
 
 int mcp_fused3d_face_tiles(int nz, int ny, int w, int dtype, int zchunk, int* counts4) {
     MCP_REQUIRE(counts4, "null argument");
-    face_tile_counts(nz, ny, w, dtype, zchunk > 0 ? zchunk : 32, counts4);
+    face_tile_counts(nz, ny, w, dtype, zchunk > 0 ? zchunk : 64, counts4);
     return MCP_OK;
 }
 
