@@ -112,6 +112,13 @@ typedef struct mcp_fused2d_desc {
     uint64_t* res_flag;                       /* local arrival counter */
     double* peer_res_inbox[MCP_MAX_RANKS];    /* [r] = rank r's ring as seen from here */
     uint64_t* peer_res_flag[MCP_MAX_RANKS];   /* [r] = rank r's counter as seen from here */
+    /* NVLS variant of the same all-reduce (takes precedence when set): a zeroed pad of 128 + 16*MCP_RES_RING bytes
+     * mapped on every rank AND bound to a multicast object; nvls_local = this rank's unicast address of its copy,
+     * nvls_mc = the multicast address.  The arrival counter is bumped on all GPUs by one multimem.red, the sum and
+     * max come back from one multimem.ld_reduce each (reduced inside NVSwitch).  The max is order independent; the
+     * sum's association order is the switch's, so use the P2P variant when bit-identical sums across ranks matter. */
+    void* nvls_local;
+    void* nvls_mc;
 } mcp_fused2d_desc;
 
 typedef struct mcp_fused2d_plan mcp_fused2d_plan;

@@ -38,6 +38,7 @@ class FusedDesc(C.Structure):
         ("world", C.c_int), ("rank", C.c_int),
         ("res_inbox", C.c_void_p), ("res_flag", C.c_void_p),
         ("peer_res_inbox", C.c_void_p * 16), ("peer_res_flag", C.c_void_p * 16),
+        ("nvls_local", C.c_void_p), ("nvls_mc", C.c_void_p),
     ]
 
 

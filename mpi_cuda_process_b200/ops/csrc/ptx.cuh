@@ -127,6 +127,21 @@ __device__ __forceinline__ void multimem_red_add_f32(float* mc, float v) {
     asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
 }
 
+__device__ __forceinline__ double multimem_ld_reduce_add_f64(const double* mc) {
+    double v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long multimem_ld_reduce_max_u64(const unsigned long long* mc) {
+    unsigned long long v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.max.u64 %0, [%1];" : "=l"(v) : "l"(mc) : "memory");
+    return v;
+}
+// one instruction adds to the same word in EVERY GPU of the multicast group (in-switch broadcast)
+__device__ __forceinline__ void multimem_red_add_release_u64(unsigned long long* mc, unsigned long long v) {
+    asm volatile("multimem.red.release.sys.global.add.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+
 // 16-byte streaming accesses (output rows are written once per sweep and not re-read by this SM).
 __device__ __forceinline__ void st_global_v4(void* p, const uint4& v) {
     asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)

@@ -74,6 +74,10 @@ struct Fused2dParams {
     // cross-rank residual all-reduce over NVLink: every rank stores its (sumsq, max) into slot [seq % ring][rank] of
     // every rank's inbox, bumps that rank's arrival counter, then sums its own inbox in rank order
     double* peer_inbox[kMaxRanks];
+    // NVLS variant: `nvls_local` is this rank's copy of a multicast-mapped pad, `nvls_mc` its multicast address
+    // (layout: u64 arrival counter @0, ring of (sumsq f64, max-bits u64) pairs @128)
+    unsigned char* nvls_local;
+    unsigned char* nvls_mc;
     unsigned long long* peer_res_flag[kMaxRanks];
     const unsigned long long* res_flag;
     unsigned long long res_seq_base;
@@ -644,7 +648,24 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     sa += red_ss[k];
                     sb = fmax(sb, red_mx[k]);
                 }
-                if (p.world > 1 && p.peer_inbox[0] != nullptr) {
+                if (p.world > 1 && p.nvls_mc != nullptr) {
+                    // NVLS all-reduce: every rank stores its pair into its OWN copy of the slot, one multimem.red
+                    // bumps the arrival counter of every GPU through the switch, and multimem.ld_reduce pulls the
+                    // sum / max of all copies through the switch in one load each.
+                    const unsigned long long seq = p.res_seq_base + (unsigned long long)sw;
+                    const size_t off = 128 + (size_t)(seq % kResRing) * 16;
+                    *reinterpret_cast<volatile double*>(p.nvls_local + off) = sa;
+                    *reinterpret_cast<volatile unsigned long long*>(p.nvls_local + off + 8) =
+                        (unsigned long long)__double_as_longlong(sb);  // sb >= 0: bit pattern order == value order
+                    ptx::fence_acq_rel_sys();
+                    ptx::multimem_red_add_release_u64(reinterpret_cast<unsigned long long*>(p.nvls_mc), 1ull);
+                    if (wait_counter_sys(p, reinterpret_cast<const unsigned long long*>(p.nvls_local),
+                                         (seq + 1ull) * (unsigned long long)p.world)) {
+                        sa = ptx::multimem_ld_reduce_add_f64(reinterpret_cast<const double*>(p.nvls_mc + off));
+                        sb = __longlong_as_double((long long)ptx::multimem_ld_reduce_max_u64(
+                            reinterpret_cast<const unsigned long long*>(p.nvls_mc + off + 8)));
+                    }
+                } else if (p.world > 1 && p.peer_inbox[0] != nullptr) {
                     // all-reduce over peer memory: push, signal, wait for everybody, sum in rank order
                     const unsigned long long seq = p.res_seq_base + (unsigned long long)sw;
                     const size_t off = ((size_t)(seq % kResRing) * kMaxRanks + (size_t)p.rank) * 2;
@@ -981,7 +1002,7 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
     while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
     if (res) pl->res_slots_used = 0;
     pl->last_generations = 0;
-    const bool exchange = d.world > 1 && d.res_inbox != nullptr;
+    const bool exchange = d.world > 1 && (d.res_inbox != nullptr || d.nvls_mc != nullptr);
 
     int remaining = generations;
     while (remaining > 0) {
@@ -1038,6 +1059,8 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
                 p.peer_inbox[r] = (double*)d.peer_res_inbox[r];
                 p.peer_res_flag[r] = (unsigned long long*)d.peer_res_flag[r];
             }
+        p.nvls_local = (unsigned char*)d.nvls_local;
+        p.nvls_mc = (unsigned char*)d.nvls_mc;
         p.stop_word = pl->stop_words;
         p.sweeps_done = pl->stop_words + 1;
         p.stop_mode = stop_mode;

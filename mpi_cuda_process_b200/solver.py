@@ -232,7 +232,23 @@ class Solver:
         d.max_ctas = int(cfg.extra.get("max_ctas", 0))
         d.world, d.rank = self.ctx.world, self.ctx.rank
         self._res_in_kernel = False
-        if self.ctx.distributed and not cfg.extra.get("host_residual", False):
+        if self.ctx.distributed and cfg.extra.get("residual_allreduce") == "nvls":
+            # NVLS variant: a multicast-mapped pad from torch's symmetric memory (bootstrap only; the reduction
+            # itself is multimem.* instructions inside the sweep kernel)
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            self._nvls_pad = symm.empty(4096, dtype=torch.uint8, device=self.ctx.device)
+            self._nvls_pad.zero_()
+            hdl = symm.rendezvous(self._nvls_pad, dist.group.WORLD.group_name)
+            if not hdl.multicast_ptr:
+                raise RuntimeError("this system exposes no multicast (NVLS) mapping")
+            torch.cuda.synchronize(self.ctx.device)
+            self.ctx.barrier()
+            d.nvls_local = self._nvls_pad.data_ptr()
+            d.nvls_mc = hdl.multicast_ptr
+            self._nvls_handle = hdl
+            self._res_in_kernel = True
+        elif self.ctx.distributed and not cfg.extra.get("host_residual", False):
             d.res_inbox = self._arena.peer_ptr(self.ctx.rank, 4096)
             d.res_flag = self._arena.peer_ptr(self.ctx.rank, 256)
             for r in range(self.ctx.world):

@@ -111,6 +111,34 @@ def main() -> int:
             ok = ctx.broadcast_object(ok, 0)
             if not ok:
                 rc = 1
+    # NVLS variant of the fused residual all-reduce (multimem.red / multimem.ld_reduce through NVSwitch)
+    if rc == 0:
+        cfg = RunConfig(workload="mdf", height=200, width=300, backend="fused", time_block=4, residual="linf",
+                        extra={"residual_allreduce": "nvls"})
+        try:
+            with Solver(cfg, ctx=ctx) as s:
+                s.initialize()
+                st = s.run(8, residual=True)
+                s.check_status()
+                u = oracle.mdf_init(200, 300)
+                exp = []
+                for gen in range(1, 9):
+                    v = oracle.mdf_step(u)
+                    if gen % 4 == 0:
+                        exp.append(oracle.residual(v, u, "linf"))
+                    u = v
+                got = [r for _, r in st.residual_history]
+                l2 = s._last_residual[0]
+                ref_l2 = float(((v.astype(np.float64) - oracle.mdf_run(oracle.mdf_init(200, 300), 7)) ** 2).sum())
+                allg = ctx.all_gather_object(got)
+                ok = all(a == exp for a in allg) and abs(l2 - ref_l2) <= 1e-6 * ref_l2
+                if ctx.rank == 0:
+                    print(json.dumps({"case": "fused residual nvls", "world": ctx.world, "ok": bool(ok)}), flush=True)
+                if not ok:
+                    rc = 1
+        except RuntimeError as e:
+            if ctx.rank == 0:
+                print(json.dumps({"case": "fused residual nvls", "skipped": str(e)[:120]}), flush=True)
     # fused gather + pack over NVLink: print_array bytes assembled on rank 0 by all ranks' pack kernels
     if rc == 0:
         from mpi_cuda_process_b200 import io as mio
