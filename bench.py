@@ -43,7 +43,7 @@ def parse_args(argv=None):
     p.add_argument("--width", type=int, default=16384)
     p.add_argument("--gens-per-step", type=int, default=1000)
     p.add_argument("--time-block", type=int, default=8)
-    p.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])
+    p.add_argument("--dtype", default="fp32", choices=["fp32", "fp64", "bits"])
     p.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                    help="weak: --height is per GPU (BASELINE.json config 4 uses 8192 x 8192 per GPU)")
     p.add_argument("--chunk-rows", type=int, default=0)
@@ -98,7 +98,8 @@ def main(argv=None) -> int:
         if args.scaling == "weak" and args.decomposition == "slab":
             depth, h = depth * ctx.world, args.height
     cfg = RunConfig(workload=args.workload, height=h, width=w, depth=depth if args.workload == "heat3d" else 0,
-                    dtype="int32" if args.workload == "life" else args.dtype, backend=backend,
+                    dtype=("bits" if args.dtype == "bits" else "int32") if args.workload == "life" else args.dtype,
+                    backend=backend,
                     decomposition=args.decomposition, seed=0 if args.workload == "life" else None,
                     time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
                     extra={"chunk_rows": args.chunk_rows})
@@ -171,9 +172,9 @@ def main(argv=None) -> int:
                    "last_residual": last, "overlap": "H2D of step i+1 overlaps compute of step i (side stream)"}
 
         if ctx.rank == 0:
-            esize = 8 if args.dtype == "fp64" else 4
+            esize = 8 if args.dtype == "fp64" else (0.125 if args.dtype == "bits" else 4)
             cells_gpu = cells // ctx.world
-            halo = 0 if ctx.world == 1 else 2 * (cells // cfg.shape[0]) * esize
+            halo = 0 if ctx.world == 1 else int(2 * (cells // cfg.shape[0]) * esize)
             roof = metrics.roofline(cells_gpu, gps * K, ms_total, 2 * esize, halo)
             out = {
                 "metric": METRIC, "value": round(value, 3), "unit": "GLUPS", "n_gpus": ctx.world, "steps": K,
@@ -187,7 +188,7 @@ def main(argv=None) -> int:
                            "iterations": gps * K, "parallelism": f"{args.decomposition}{ctx.world}",
                            "time_block": s.time_block, "backend": s.backend,
                            "l2": "inputs larger than L2 (two %d MiB buffers per GPU stream through HBM every pass)"
-                                 % (cells_gpu * esize >> 20), "geometry": geom},
+                                 % (int(cells_gpu * esize) >> 20), "geometry": geom},
                 "gpu_launches": int(launches),
                 "clocks": clocks,
                 "roofline": {k: (round(v, 4) if isinstance(v, float) else v) for k, v in roof.items()},

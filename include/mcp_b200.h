@@ -21,6 +21,7 @@ extern "C" {
 #define MCP_DTYPE_F32 0
 #define MCP_DTYPE_F64 1
 #define MCP_DTYPE_I32 2
+#define MCP_DTYPE_B1 3  /* bit-packed cells: 32 per 32-bit word, cell x = bit x%32 of word x/32 (life only) */
 
 /* stencil operators */
 #define MCP_OP_MDF 0  /* 2-D 5-point heat/Jacobi update, M:10-22 */
@@ -63,6 +64,9 @@ int mcp_init_shape2d(int dtype, int kind, void* u_dev, int64_t pitch, int rows_a
 /* Seeded synthetic life field: ring dead, interior alive iff hash32(i*w+j, seed) < prob * 2^32. */
 int mcp_init_life_hash(int32_t* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double prob,
                        uint32_t seed, void* stream);
+/* Same field, bit-packed (MCP_DTYPE_B1): pitch in 32-bit words. */
+int mcp_init_life_hash_bits(uint32_t* u_dev, int64_t pitch_words, int rows_alloc, int row0, int h, int w, double prob,
+                            uint32_t seed, void* stream);
 /* Re-impose the fixed ring on owned rows (the "else -> 100 / 0" branches of M:35,43,59,67, K:86,102,110). */
 int mcp_apply_ring2d(int dtype, void* u_dev, int64_t pitch, int rows_alloc, int row0, int h, int w, double ring,
                      void* stream);
@@ -92,7 +96,7 @@ typedef struct mcp_fused2d_desc {
     int row_start;   /* first owned global row */
     int rows_own;    /* owned rows */
     int ghost;       /* ghost rows above and below the owned rows in every buffer (>= time_block) */
-    int64_t pitch;   /* elements per row, multiple of 32 */
+    int64_t pitch;   /* storage elements per row, multiple of 32 (MCP_DTYPE_B1: 32-bit words of 32 cells) */
     void* buf[2];    /* local double buffer, each (ghost + rows_own + ghost) x pitch */
     void* up_buf[2]; /* rank-1's buffers mapped into this process, or NULL at the top of the chain */
     void* dn_buf[2]; /* rank+1's buffers, or NULL at the bottom */

@@ -48,7 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--height", type=int, default=None)
     p.add_argument("--width", type=int, default=None)
     p.add_argument("--depth", type=int, default=0)
-    p.add_argument("--dtype", choices=["fp32", "fp64"], default="fp32")
+    p.add_argument("--dtype", choices=["fp32", "fp64", "bits"], default="fp32",
+                   help="bits = bit-packed life cells (fused GPU backend)")
     p.add_argument("--bc", choices=["fixed-ring", "dead-outside"], default=None)
     p.add_argument("--backend", choices=["auto", "fused", "nccl", "staged", "cpu"], default="auto")
     p.add_argument("--decomposition", choices=["slab", "pencil"], default="slab")
@@ -98,7 +99,7 @@ def main(argv: Optional[List[str]] = None) -> int:
 
     cfg = RunConfig(
         workload=args.workload, generations=g, height=h, width=w, depth=args.depth,
-        dtype="int32" if args.workload == "life" else args.dtype,
+        dtype=("bits" if args.dtype == "bits" else "int32") if args.workload == "life" else args.dtype,
         bc=args.bc,
         ring=args.ring, interior=args.interior, prob=args.prob, init=args.init, seed=args.seed, backend=args.backend,
         decomposition=args.decomposition, pencil=tuple(args.pencil), time_block=args.time_block, tol=args.tol,

@@ -16,7 +16,7 @@ from typing import Optional, Tuple
 
 WORKLOADS = ("mdf", "life", "heat3d")
 BACKENDS = ("auto", "fused", "nccl", "staged", "cpu")
-DTYPES = ("fp32", "fp64", "int32")
+DTYPES = ("fp32", "fp64", "int32", "bits")
 BC_MODES = ("fixed-ring", "dead-outside")
 
 
@@ -92,9 +92,10 @@ class RunConfig:
         if self.bc not in BC_MODES:
             raise ValueError(f"bc must be one of {BC_MODES}, got {self.bc!r}")
         if self.workload == "life":
-            self.dtype = "int32"
-        elif self.dtype == "int32":
-            raise ValueError("int32 is only valid for the life workload")
+            if self.dtype != "bits":        # "bits" = one cell per bit (fused GPU backend only); default int32 cells
+                self.dtype = "int32"
+        elif self.dtype in ("int32", "bits"):
+            raise ValueError(f"{self.dtype} is only valid for the life workload")
         if self.workload == "heat3d" and self.depth <= 0:
             raise ValueError("heat3d needs depth > 0")
         if self.workload != "heat3d" and self.depth not in (0, 1):

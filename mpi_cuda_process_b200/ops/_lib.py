@@ -84,6 +84,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_init_ring2d.argtypes = [i, vp, i64, i, i, i, i, dbl, dbl, vp]
     lib.mcp_init_shape2d.argtypes = [i, i, vp, i64, i, i, i, i, dbl, dbl, u32, vp]
     lib.mcp_init_life_hash.argtypes = [vp, i64, i, i, i, i, dbl, u32, vp]
+    lib.mcp_init_life_hash_bits.argtypes = [vp, i64, i, i, i, i, dbl, u32, vp]
     lib.mcp_apply_ring2d.argtypes = [i, vp, i64, i, i, i, i, dbl, vp]
     lib.mcp_init_shell3d.argtypes = [i, vp, i64, i64, i, i, i, i, i, i, i, dbl, dbl, vp]
     lib.mcp_step2d.argtypes = [i, i, vp, vp, i64, i, i, i, i, i, i, i, i, i, i, vp]

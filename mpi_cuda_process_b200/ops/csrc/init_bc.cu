@@ -47,6 +47,26 @@ __global__ void init_life_hash_kernel(int* __restrict__ u, long long pitch, int 
     }
 }
 
+// Bit-packed variant of init_life_hash_kernel: one thread builds one 32-cell word (cell x = bit x%32 of word x/32).
+__global__ void init_life_hash_bits_kernel(unsigned* __restrict__ u, long long pitch, int rows_alloc, int row0, int h,
+                                           int w, unsigned thr, unsigned seed) {
+    const long long n = (long long)rows_alloc * pitch;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(i / pitch), e = (int)(i - (long long)r * pitch);
+        const int gy = row0 + r;
+        unsigned word = 0u;
+        if (gy > 0 && gy < h - 1) {
+#pragma unroll 8
+            for (int b = 0; b < 32; ++b) {
+                const int c = e * 32 + b;
+                if (c > 0 && c < w - 1 && hash32((unsigned)((long long)gy * w + c), seed) < thr) word |= 1u << b;
+            }
+        }
+        u[i] = word;
+    }
+}
+
 // Synthetic initial fields beyond the reference's ring (all exactly reproducible on the host, oracle.py):
 // kind 1: interior cells uniform in [interior, ring) from hash32(i*w+j, seed) (24 random bits);
 // kind 2: a hot box (value ring) over the central third of the domain, interior elsewhere.  Ring = ring either way.
@@ -167,6 +187,18 @@ int mcp_init_life_hash(int32_t* u, int64_t pitch, int rows_alloc, int row0, int 
     const unsigned thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (t <= 0 ? 0u : (unsigned)t);
     const long long n = (long long)rows_alloc * pitch;
     init_life_hash_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(u, pitch, rows_alloc, row0, h, w, thr, seed);
+    MCP_CUDA_TRY(cudaGetLastError());
+    return MCP_OK;
+}
+
+int mcp_init_life_hash_bits(uint32_t* u, int64_t pitch_words, int rows_alloc, int row0, int h, int w, double prob,
+                            uint32_t seed, void* stream) {
+    MCP_REQUIRE(u && pitch_words * 32 >= w && rows_alloc > 0, "mcp_init_life_hash_bits: bad arguments");
+    double t = prob * 4294967296.0;
+    const unsigned thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (t <= 0 ? 0u : (unsigned)t);
+    const long long n = (long long)rows_alloc * pitch_words;
+    init_life_hash_bits_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(u, pitch_words, rows_alloc, row0, h, w,
+                                                                              thr, seed);
     MCP_CUDA_TRY(cudaGetLastError());
     return MCP_OK;
 }

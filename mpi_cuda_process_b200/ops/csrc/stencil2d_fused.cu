@@ -49,9 +49,11 @@ constexpr int kSmemBytes = smem_bytes_for(kWarpsPerCta);
 // TB = 8 keeps 96 registers of row windows per thread: run 12 warps x 168 registers instead of 16 x 128.
 constexpr int kWarpsTb8 = 8;
 __host__ __device__ constexpr int warps_for_tb(int tb) { return tb >= 8 ? kWarpsTb8 : kWarpsPerCta; }
-// Life keeps cells and horizontal sums per window row (24 registers per level): TB = 4 also needs the wide budget.
-__host__ __device__ constexpr int warps_for(bool is_life, int tb) {
-    return (is_life && tb >= 4) ? kWarpsTb8 : warps_for_tb(tb);
+// Register budget per operator: kind 0 = scalar float cells (12 window registers per level), 1 = Life int32 (cells
+// + horizontal sums, 24 per level), 2 = bit-packed Life (cells + two sum planes, 36 per level).  When the windows of
+// TB levels no longer fit 128 registers the CTA runs 8 warps x up to 255 registers instead of 16 x 128.
+__host__ __device__ constexpr int warps_for(int kind, int tb) {
+    return (kind == 2 && tb >= 2) || (kind == 1 && tb >= 4) ? kWarpsTb8 : warps_for_tb(tb);
 }
 constexpr int kMaxResSlots = 16384;
 constexpr int kMaxRanks = MCP_MAX_RANKS;
@@ -103,7 +105,26 @@ struct Fused2dParams {
 
 // ------------------------------------------------------------------------------------------ operators
 
-struct MdfF32 {
+// Column masks of the scalar-cell operators: one bit per vector component.
+template <int VEC_>
+struct ComponentMask {
+    using Mask = unsigned;
+    static constexpr int CPE = 1;  // cells per storage element
+    static __device__ __forceinline__ Mask full_mask() { return 0xfu; }
+    static __device__ __forceinline__ bool any(Mask m) { return m != 0u; }
+    // component v of the lane's vector is cell cx + v
+    static __device__ __forceinline__ Mask col_mask(int cx, int xlo, int xhi) {
+        Mask m = 0;
+#pragma unroll
+        for (int v = 0; v < VEC_; ++v) {
+            const int gx = cx + v;
+            if (gx < xlo || gx > xhi) m |= 1u << v;
+        }
+        return m;
+    }
+};
+
+struct MdfF32 : ComponentMask<4> {
     using T = float;
     using V = float4;
     static constexpr int VEC = 4;
@@ -144,7 +165,7 @@ struct MdfF32 {
     }
 };
 
-struct MdfF64 {
+struct MdfF64 : ComponentMask<2> {
     using T = double;
     using V = double2;
     static constexpr int VEC = 2;
@@ -173,7 +194,7 @@ struct MdfF64 {
     }
 };
 
-struct LifeI32 {
+struct LifeI32 : ComponentMask<4> {
     using T = int;
     using V = int4;
     static constexpr int VEC = 4;
@@ -214,6 +235,87 @@ struct LifeI32 {
         const int d0 = a.x - b.x, d1 = a.y - b.y, d2 = a.z - b.z, d3 = a.w - b.w;
         const int q = d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
         ss += (double)q;
+        mx = fmax(mx, q ? 1.0 : 0.0);
+    }
+};
+
+// Bit-packed Game of Life: one cell per bit, 32 cells per 32-bit word (cell x = bit x%32 of word x/32), so a lane's
+// 16-byte vector holds 128 cells and a warp row 4096.  Same rule as LifeI32 (kernel.cu:61,66), evaluated for 32 cells
+// at a time with bit-sliced adders.  The optional fast path of SURVEY section 7.1; the reference stores one int per cell.
+struct LifeB1 {
+    using T = unsigned;
+    using V = uint4;
+    static constexpr int VEC = 4;   // storage elements per lane
+    static constexpr int CPE = 32;  // cells per storage element
+    using Mask = uint4;             // one bit per cell: 1 = keep the old value
+    struct Row {
+        V v;       // cells
+        V s0, s1;  // per cell: (s1:s0) = west + self + east (0..3)
+    };
+    static __device__ __forceinline__ Mask full_mask() {
+        return make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    }
+    static __device__ __forceinline__ bool any(const Mask& m) { return (m.x | m.y | m.z | m.w) != 0u; }
+    // bits of the word holding cells [c0, c0+32) that lie outside [xlo, xhi]
+    static __device__ __forceinline__ unsigned word_mask(int c0, int xlo, int xhi) {
+        unsigned keep = 0u;  // bits inside [xlo, xhi] -> evolve
+        const int lo = max(xlo, c0), hi = min(xhi, c0 + 31);
+        if (lo <= hi) {
+            const int n = hi - lo + 1;
+            const unsigned run = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+            keep = run << (lo - c0);
+        }
+        return ~keep;
+    }
+    static __device__ __forceinline__ Mask col_mask(int cx, int xlo, int xhi) {
+        // cx = index of the lane's first storage element; element e holds cells 32e .. 32e+31
+        return make_uint4(word_mask((cx + 0) * 32, xlo, xhi), word_mask((cx + 1) * 32, xlo, xhi),
+                          word_mask((cx + 2) * 32, xlo, xhi), word_mask((cx + 3) * 32, xlo, xhi));
+    }
+    static __device__ __forceinline__ unsigned maj(unsigned a, unsigned b, unsigned c) { return (a & b) | (c & (a ^ b)); }
+    static __device__ __forceinline__ Row make_row(const V& raw) {
+        const unsigned prevw = __shfl_up_sync(0xffffffffu, raw.w, 1);    // word to the west of .x
+        const unsigned nextx = __shfl_down_sync(0xffffffffu, raw.x, 1);  // word to the east of .w
+        Row r;
+        r.v = raw;
+        const unsigned c[4] = {raw.x, raw.y, raw.z, raw.w};
+        const unsigned wprev[4] = {prevw, raw.x, raw.y, raw.z};
+        const unsigned enext[4] = {raw.y, raw.z, raw.w, nextx};
+        unsigned s0[4], s1[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned W = (c[k] << 1) | (wprev[k] >> 31);  // west neighbour of every cell of the word
+            const unsigned E = (c[k] >> 1) | (enext[k] << 31);  // east neighbour
+            s0[k] = W ^ c[k] ^ E;
+            s1[k] = maj(W, c[k], E);
+        }
+        r.s0 = make_uint4(s0[0], s0[1], s0[2], s0[3]);
+        r.s1 = make_uint4(s1[0], s1[1], s1[2], s1[3]);
+        return r;
+    }
+    static __device__ __forceinline__ unsigned word(unsigned n0, unsigned n1, unsigned c0, unsigned c1, unsigned s0,
+                                                    unsigned s1, unsigned centre) {
+        // total (0..9, centre included) = l + 2*t1 + 4*t2 + 8*t3
+        const unsigned l = n0 ^ c0 ^ s0, cl = maj(n0, c0, s0);
+        const unsigned h = n1 ^ c1 ^ s1, ch = maj(n1, c1, s1);
+        const unsigned t1 = h ^ cl, c2 = h & cl;
+        const unsigned t2 = ch ^ c2, t3 = ch & c2;
+        // alive next iff total == 3, or total == 4 and alive now  (= 3 neighbours, or 2 neighbours and alive)
+        return ~t3 & ((l & t1 & ~t2) | (~l & ~t1 & t2 & centre));
+    }
+    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
+        return make_uint4(word(n.s0.x, n.s1.x, c.s0.x, c.s1.x, s.s0.x, s.s1.x, c.v.x),
+                          word(n.s0.y, n.s1.y, c.s0.y, c.s1.y, s.s0.y, s.s1.y, c.v.y),
+                          word(n.s0.z, n.s1.z, c.s0.z, c.s1.z, s.s0.z, s.s1.z, c.v.z),
+                          word(n.s0.w, n.s1.w, c.s0.w, c.s1.w, s.s0.w, s.s1.w, c.v.w));
+    }
+    static __device__ __forceinline__ V select(const Mask& m, const V& keep, const V& upd) {
+        return make_uint4((keep.x & m.x) | (upd.x & ~m.x), (keep.y & m.y) | (upd.y & ~m.y),
+                          (keep.z & m.z) | (upd.z & ~m.z), (keep.w & m.w) | (upd.w & ~m.w));
+    }
+    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
+        const int q = __popc(a.x ^ b.x) + __popc(a.y ^ b.y) + __popc(a.z ^ b.z) + __popc(a.w ^ b.w);
+        ss += (double)q;  // changed cells: (a-b)^2 is 0 or 1
         mx = fmax(mx, q ? 1.0 : 0.0);
     }
 };
@@ -308,7 +410,8 @@ template <class Op, int TB, int MODE, bool RES>
 __device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const uint8_t* sp,
                                            typename Op::T*& optr, const long long pitch, const int cbase,
                                            const int n_in, const int gy_base, const int ylo, const int yhi,
-                                           const unsigned colfix, const bool lane_valid, const bool lane_store,
+                                           const typename Op::Mask colfix, const bool lane_valid,
+                                           const bool lane_store,
                                            double& rs, double& rm) {
     using V = typename Op::V;
     constexpr bool GENERAL = (MODE == 2);
@@ -324,7 +427,7 @@ __device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const u
             V res = Op::update(L[t - 1][sn], L[t - 1][sc], L[t - 1][ss]);
             if (GENERAL) {
                 const int gy = gy_base + j - t;
-                const unsigned m = (gy < ylo || gy > yhi) ? 0xfu : colfix;
+                const typename Op::Mask m = (gy < ylo || gy > yhi) ? Op::full_mask() : colfix;
                 res = Op::select(m, L[t - 1][sc].v, res);
             } else if (MODE == 1) {
                 res = Op::select(colfix, L[t - 1][sc].v, res);
@@ -356,21 +459,17 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
     using T = typename Op::T;
     using V = typename Op::V;
     using Row = typename Op::Row;
-    constexpr int VEC = Op::VEC;
-    constexpr int M = (TB + VEC - 1) / VEC;  // margin lanes whose cells go stale within TB levels
+    constexpr int VEC = Op::VEC;  // storage elements per lane (x_ld, cx, pitch are in elements)
+    constexpr int CPE = Op::CPE;  // cells per element (32 for the bit-packed operator)
+    constexpr int M = (TB + VEC * CPE - 1) / (VEC * CPE);  // margin lanes whose cells go stale within TB levels
 
     const int ys = y0 - TB;
     const int n_in = (y1 - y0) + 2 * TB;
     const int n_it = (n_in + kRowsPerStage - 1) / kRowsPerStage;
     const int cx = x_ld + lane * VEC;
 
-    unsigned colfix = 0;
-#pragma unroll
-    for (int v = 0; v < VEC; ++v) {
-        const int gx = cx + v;
-        if (gx < p.xlo || gx > p.xhi) colfix |= 1u << v;
-    }
-    const bool col_masked = (x_ld < p.xlo) || (x_ld + 32 * VEC - 1 > p.xhi);
+    const typename Op::Mask colfix = Op::col_mask(cx, p.xlo, p.xhi);
+    const bool col_masked = (x_ld * CPE < p.xlo) || ((x_ld + 32 * VEC) * CPE - 1 > p.xhi);
     const bool lane_valid = (lane >= M) && (lane < 32 - M);
     const bool lane_store = lane_valid && (cx < (int)p.pitch);
 
@@ -480,8 +579,8 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ Fused2dParams p) {
     using T = typename Op::T;
     constexpr int VEC = Op::VEC;
-    constexpr int M = (TB + VEC - 1) / VEC;
-    constexpr int OUTW = (32 - 2 * M) * VEC;
+    constexpr int M = (TB + VEC * Op::CPE - 1) / (VEC * Op::CPE);
+    constexpr int OUTW = (32 - 2 * M) * VEC;  // storage elements written per strip
 
     extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -741,9 +840,14 @@ namespace {
 
 int vec_of(int dtype) { return dtype == MCP_DTYPE_F64 ? 2 : 4; }
 
+int op_kind(const mcp_fused2d_desc& d) { return d.dtype == MCP_DTYPE_B1 ? 2 : (d.op == MCP_OP_LIFE ? 1 : 0); }
+
+int cpe_of(int dtype) { return dtype == MCP_DTYPE_B1 ? 32 : 1; }  // cells per storage element
+
+// output columns (cells) per strip
 int outw_rt(int dtype, int tb) {
-    const int vec = vec_of(dtype);
-    return (32 - 2 * ((tb + vec - 1) / vec)) * vec;
+    const int vec = vec_of(dtype), cpe = cpe_of(dtype);
+    return (32 - 2 * ((tb + vec * cpe - 1) / (vec * cpe))) * vec * cpe;
 }
 
 int max_tb(int op, int dtype) {
@@ -798,7 +902,7 @@ void build_chunks(const mcp_fused2d_plan* pl, int tb, std::vector<int>* out, int
         for (int c = 1; c <= nc; ++c) y.push_back(own_lo + (int)((long long)rows * c / nc));
         return;
     }
-    const int NW = pl->grid * warps_for(d.op == MCP_OP_LIFE, tb);
+    const int NW = pl->grid * warps_for(op_kind(d), tb);
     const char* e_k = getenv("MCP_GSS_K");
     const char* e_rmin = getenv("MCP_GSS_RMIN");
     const char* e_rmax = getenv("MCP_GSS_RMAX");
@@ -837,7 +941,7 @@ void choose_geometry(const mcp_fused2d_plan* pl, int tb, int* n_strips, int* n_c
 
 template <class Op, int TB>
 int launch_variant(mcp_fused2d_plan* pl, const Fused2dParams& p, bool res, cudaStream_t stream) {
-    constexpr int W = warps_for(std::is_same<Op, LifeI32>::value, TB);
+    constexpr int W = warps_for(std::is_same<Op, LifeB1>::value ? 2 : (std::is_same<Op, LifeI32>::value ? 1 : 0), TB);
     constexpr int smem = smem_bytes_for(W);
     void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
     const void* fn = res ? (const void*)fused2d_kernel<Op, TB, true, W> : (const void*)fused2d_kernel<Op, TB, false, W>;
@@ -867,6 +971,7 @@ int launch_any(mcp_fused2d_plan* pl, int tb, const Fused2dParams& p, bool res, c
     }
     if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F64) return launch_tb<MdfF64>(pl, tb, p, res, stream);
     if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_I32) return launch_tb<LifeI32>(pl, tb, p, res, stream);
+    if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_B1) return launch_tb<LifeB1>(pl, tb, p, res, stream);
     set_error("unsupported op/dtype combination %d/%d", d.op, d.dtype);
     return MCP_ERR_UNSUPPORTED;
 }
@@ -879,10 +984,12 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     MCP_REQUIRE(desc && plan_out, "mcp_fused2d_create: null argument");
     const mcp_fused2d_desc& d = *desc;
     MCP_REQUIRE(d.op == MCP_OP_MDF || d.op == MCP_OP_LIFE, "bad op %d", d.op);
-    MCP_REQUIRE((d.op == MCP_OP_LIFE) == (d.dtype == MCP_DTYPE_I32), "op %d does not take dtype %d", d.op, d.dtype);
+    MCP_REQUIRE((d.op == MCP_OP_LIFE) == (d.dtype == MCP_DTYPE_I32 || d.dtype == MCP_DTYPE_B1),
+                "op %d does not take dtype %d", d.op, d.dtype);
     MCP_REQUIRE(d.h >= 1 && d.w >= 1 && d.rows_own >= 1, "empty grid");
     MCP_REQUIRE(d.ghost >= 1 && d.ghost <= 8, "ghost depth %d outside [1,8]", d.ghost);
-    MCP_REQUIRE(d.pitch >= d.w && d.pitch % 32 == 0, "pitch %lld must be a multiple of 32 and >= w", (long long)d.pitch);
+    MCP_REQUIRE(d.pitch * cpe_of(d.dtype) >= d.w && d.pitch % 32 == 0,
+                "pitch %lld (elements) must be a multiple of 32 and cover w", (long long)d.pitch);
     MCP_REQUIRE(d.buf[0] && d.buf[1], "null field buffer");
     MCP_REQUIRE(((uintptr_t)d.buf[0] % 128 == 0) && ((uintptr_t)d.buf[1] % 128 == 0), "buffers must be 128-byte aligned");
     MCP_REQUIRE((d.up_buf[0] == nullptr) == (d.up_buf[1] == nullptr), "up_buf must be both set or both null");
@@ -925,7 +1032,8 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         uint64_t dims[2] = {(uint64_t)d.pitch, (uint64_t)pl->rows_alloc};
         uint64_t strides[1] = {(uint64_t)d.pitch * esz};
         uint32_t box[2] = {(uint32_t)(kRowBytes / esz), (uint32_t)kRowsPerStage};
-        rc = encode_tensor_map(&pl->tm[b], d.dtype, 2, d.buf[b], dims, strides, box);
+        rc = encode_tensor_map(&pl->tm[b], d.dtype == MCP_DTYPE_B1 ? (int)MCP_DTYPE_I32 : d.dtype, 2, d.buf[b], dims,
+                               strides, box);
         if (rc) { delete pl; return rc; }
     }
     // scratch: grid barrier counter, status word, residual partials + history
@@ -982,7 +1090,7 @@ int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_stri
     if (n_strips) *n_strips = ns;
     if (n_chunks) *n_chunks = nc;
     if (grid) *grid = pl->grid;
-    if (smem_bytes) *smem_bytes = smem_bytes_for(warps_for(pl->d.op == MCP_OP_LIFE, time_block));
+    if (smem_bytes) *smem_bytes = smem_bytes_for(warps_for(op_kind(pl->d), time_block));
     return MCP_OK;
 }
 
@@ -1070,7 +1178,7 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
         // pays when a warp has few tiles per sweep; with many tiles per warp the plain barrier is cheaper.
         int sync_mode = pl->sync_mode;
         if (sync_mode == 0) {
-            const double tiles_per_warp = (double)ns * nc / ((double)pl->grid * warps_for(d.op == MCP_OP_LIFE, tb));
+            const double tiles_per_warp = (double)ns * nc / ((double)pl->grid * warps_for(op_kind(d), tb));
             sync_mode = (tb < 8 || tiles_per_warp < 5.0) ? 2 : 1;
         }
         if (res) sync_mode = 1;
@@ -1089,7 +1197,7 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
             executed = words[1];
             MCP_REQUIRE(executed >= 0 && executed <= sweeps, "device reported %d executed sweeps of %d", executed, sweeps);
         }
-        const unsigned long long nw = (unsigned long long)pl->grid * warps_for(d.op == MCP_OP_LIFE, tb);
+        const unsigned long long nw = (unsigned long long)pl->grid * warps_for(op_kind(d), tb);
         if (sync_mode == 1) {
             const unsigned long long barriers = res ? (unsigned long long)executed : (unsigned long long)(executed - 1);
             pl->bar_base += barriers * (unsigned long long)pl->grid;

@@ -31,9 +31,9 @@ from .parallel.context import DistContext, init_context
 from .parallel.decomp import Decomposition
 from .parallel import host_p2p
 
-_TORCH_DTYPE = {"fp32": torch.float32, "fp64": torch.float64, "int32": torch.int32}
-_NP_DTYPE = {"fp32": np.float32, "fp64": np.float64, "int32": np.int32}
-_MCP_DTYPE = {"fp32": 0, "fp64": 1, "int32": 2}
+_TORCH_DTYPE = {"fp32": torch.float32, "fp64": torch.float64, "int32": torch.int32, "bits": torch.int32}
+_NP_DTYPE = {"fp32": np.float32, "fp64": np.float64, "int32": np.int32, "bits": np.int32}
+_MCP_DTYPE = {"fp32": 0, "fp64": 1, "int32": 2, "bits": 3}
 _MCP_OP = {"mdf": 0, "life": 1}
 
 
@@ -63,6 +63,9 @@ class Solver:
         self._own_ctx = ctx is None
         self.ctx = ctx if ctx is not None else init_context(device="cpu" if cfg.backend == "cpu" else device)
         self.backend = self._pick_backend()
+        self.bits = cfg.dtype == "bits"          # bit-packed life: 32 cells per stored 32-bit word
+        if self.bits and self.backend != "fused":
+            raise ValueError("dtype='bits' (bit-packed life) runs on the fused GPU backend only")
         self.ndim = cfg.ndim
         self.tdtype = _TORCH_DTYPE[cfg.dtype]
         self.npdtype = _NP_DTYPE[cfg.dtype]
@@ -70,6 +73,8 @@ class Solver:
         # ghost depth: the fused kernel exchanges `time_block` rows every `time_block` generations
         if self.backend == "fused" and self.ndim == 2:
             tbmax = 8 if (cfg.workload == "mdf" and cfg.dtype == "fp32") else 4
+            if self.bits:
+                tbmax = 2      # measured: 24.4 TLUPS at TB=2 vs 16.3 at TB=4 (36 window registers per level)
             tb = 1
             while tb * 2 <= min(cfg.time_block, tbmax):
                 tb *= 2
@@ -130,7 +135,7 @@ class Solver:
         if self.ctx.is_cuda:
             from .ops import _lib
             self._lib = _lib.cuda_lib()
-            self.pitch = _round_up(cfg.width, 32)
+            self.pitch = _round_up((cfg.width + 31) // 32, 32) if self.bits else _round_up(cfg.width, 32)
         else:
             self.pitch = cfg.width
         store_shape = self.alloc_shape[:-1] + (self.pitch,)
@@ -291,7 +296,10 @@ class Solver:
         for b in self.bufs:
             if self.ndim == 2:
                 row0 = self.block.start[0] - G
-                if cfg.workload == "life":
+                if self.bits:
+                    _lib.check(self._lib.mcp_init_life_hash_bits(b.data_ptr(), self.pitch, self.store_shape[0], row0,
+                                                                 cfg.height, cfg.width, cfg.prob, cfg.seed, s))
+                elif cfg.workload == "life":
                     _lib.check(self._lib.mcp_init_life_hash(b.data_ptr(), self.pitch, self.store_shape[0], row0,
                                                             cfg.height, cfg.width, cfg.prob, cfg.seed, s))
                 elif cfg.workload == "mdf" and cfg.init != "ring":
@@ -315,7 +323,8 @@ class Solver:
     def _local_from_global(self, field: np.ndarray) -> np.ndarray:
         """This rank's allocation (owned block + ghost layers, zero outside the domain) cut from a global array."""
         G = self.ghost
-        loc = np.zeros(self.store_shape, dtype=self.npdtype)
+        cells_shape = self.store_shape[:-1] + (self.cfg.width,) if self.bits else self.store_shape
+        loc = np.zeros(cells_shape, dtype=self.npdtype)
         src_sl, dst_sl = [], []
         for a in range(self.ndim - 1):
             s, e = self.block.start[a] - G, self.block.stop[a] + G
@@ -325,7 +334,18 @@ class Solver:
         src_sl.append(slice(0, self.cfg.width))
         dst_sl.append(slice(0, self.cfg.width))
         loc[tuple(dst_sl)] = field[tuple(src_sl)]
-        return loc
+        return self._pack_bits(loc) if self.bits else loc
+
+    def _pack_bits(self, cells: np.ndarray) -> np.ndarray:
+        """(rows, w) cells in {0,1} -> (rows, pitch) int32 words, cell x = bit x%32 of word x//32."""
+        b = np.packbits((cells != 0).astype(np.uint8), axis=-1, bitorder="little")
+        out = np.zeros(cells.shape[:-1] + (self.pitch * 4,), dtype=np.uint8)
+        out[..., :b.shape[-1]] = b
+        return out.view("<u4").astype(np.uint32).view(np.int32).reshape(cells.shape[:-1] + (self.pitch,))
+
+    def _unpack_bits(self, words: np.ndarray) -> np.ndarray:
+        b = np.ascontiguousarray(words).view(np.uint8)
+        return np.unpackbits(b, axis=-1, bitorder="little")[..., :self.cfg.width].astype(np.int32)
 
     def load_global(self, field: np.ndarray) -> None:
         if tuple(field.shape) != tuple(self.cfg.shape):
@@ -758,6 +778,10 @@ class Solver:
     def local_owned(self) -> torch.Tensor:
         """View of this rank's owned cells in the current buffer (no ghosts, no pad)."""
         G = self.ghost
+        if self.bits:
+            torch.cuda.synchronize(self.ctx.device)
+            words = self.bufs[self.cur][G:G + self.own_shape[0]].cpu().numpy()
+            return torch.from_numpy(self._unpack_bits(words))
         sl = tuple(slice(G, G + n) for n in self.own_shape[:-1]) + (slice(0, self.cfg.width),)
         return self.bufs[self.cur][sl]
 
@@ -768,9 +792,11 @@ class Solver:
         casts fp64 -> fp32) while storing its block straight into rank 0's output buffer over NVLink; no
         intermediate copies, no NCCL.  The reference has no gather: every rank holds (a stale copy of) the whole
         grid (MDF_kernel.cu:137-144)."""
-        if self.ctx.is_cuda:
+        if self.ctx.is_cuda and not self.bits:
             return self._gather_p2p(as_fp32)
         loc = self.local_owned()
+        if self.ctx.is_cuda:
+            torch.cuda.synchronize(self.ctx.device)
         arr = loc.detach().cpu().contiguous().numpy()
         if not self.ctx.distributed:
             return arr.copy()
@@ -821,7 +847,7 @@ class Solver:
         GPUs -- every rank packs its rows to '0' / ' ' / newline bytes straight into rank 0's buffer."""
         if self.cfg.workload != "life":
             raise ValueError("print_array takes int grids only (it cannot print the float field, SURVEY D16)")
-        if not self.ctx.is_cuda:
+        if not self.ctx.is_cuda or self.bits:
             from . import io as mio
             f = self.gather()
             return mio.format_array(f) if f is not None else None

@@ -25,6 +25,8 @@ CASES = [
     dict(workload="mdf", height=300, width=260, backend="fused", time_block=4, g=37, dtype="fp64"),
     dict(workload="life", height=300, width=260, backend="fused", time_block=4, g=50),
     dict(workload="life", height=300, width=260, backend="fused", time_block=2, g=21, bc="fixed-ring"),
+    dict(workload="life", dtype="bits", height=300, width=4500, backend="fused", time_block=4, g=50),
+    dict(workload="life", dtype="bits", height=130, width=260, backend="fused", time_block=2, g=21, bc="fixed-ring"),
     dict(workload="mdf", height=263, width=389, backend="nccl", g=9),
     dict(workload="mdf", height=64, width=48, backend="staged", g=5),
     dict(workload="mdf", height=40, width=24, backend="staged", g=3, halo_message="element"),

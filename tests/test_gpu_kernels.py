@@ -331,3 +331,29 @@ def test_device_init_shapes_and_run(init, dtype):
         assert s.gather().tobytes() == f0.tobytes()
         s.run(13)
         assert s.gather().tobytes() == oracle.mdf_run(f0, 13).tobytes()
+
+
+@pytest.mark.parametrize("bc", ["dead-outside", "fixed-ring"])
+@pytest.mark.parametrize("tb", [1, 2, 4])
+@pytest.mark.parametrize("h,w,g", [(40, 70, 12), (150, 275, 23), (64, 4000, 9), (300, 4100, 14)])
+def test_life_bit_packed_exact(bc, tb, h, w, g):
+    """One cell per bit, 128 cells per lane: same generations as the int32 oracle, cell for cell."""
+    f = (np.random.default_rng(h + w).random((h, w)) < 0.4).astype(np.int32)
+    cfg = RunConfig(workload="life", dtype="bits", height=h, width=w, backend="fused", bc=bc, time_block=tb)
+    with Solver(cfg) as s:
+        s.initialize(f)
+        st = s.run(g, residual=True)
+        s.check_status()
+        ref_prev = oracle.life_run(f, g - 1, bc)
+        ref = oracle.life_step(ref_prev, bc)
+        assert (s.gather() == ref).all()
+        assert s._last_residual[0] == float((ref != ref_prev).sum())         # changed cells in the last generation
+
+
+def test_life_bit_packed_device_init_matches_hash_oracle():
+    cfg = RunConfig(workload="life", dtype="bits", height=77, width=391, backend="fused", seed=5, time_block=2)
+    with Solver(cfg) as s:
+        s.initialize()
+        assert (s.gather() == oracle.life_init_hash(77, 391, 0.15, 5)).all()
+        s.run(6)
+        assert (s.gather() == oracle.life_run(oracle.life_init_hash(77, 391, 0.15, 5), 6)).all()
