@@ -137,6 +137,9 @@ int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int
  * generation count only (M:153,157,186). */
 int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* plan, int max_generations, int time_block, int norm, double tol,
                                  int* generations_done, void* stream);
+/* Protocol check: the number of halo arrivals this rank should have received so far from rank-1 and rank+1.
+ * After a synchronised run the local counters flags[0], flags[1] must equal these (when that neighbour exists). */
+int mcp_fused2d_expected_flags(const mcp_fused2d_plan* plan, uint64_t* up_dn);
 int mcp_fused2d_parity(const mcp_fused2d_plan* plan);
 int mcp_fused2d_set_parity(mcp_fused2d_plan* plan, int parity);
 /* Residual history of the last run with MCP_RES_LAST: per time block (sum of squares, max abs) of u' - u --

@@ -1239,6 +1239,13 @@ int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int 
     return rc;
 }
 
+int mcp_fused2d_expected_flags(const mcp_fused2d_plan* pl, uint64_t* up_dn) {
+    MCP_REQUIRE(pl && up_dn, "null argument");
+    up_dn[0] = pl->flag_base_up;
+    up_dn[1] = pl->flag_base_dn;
+    return MCP_OK;
+}
+
 int mcp_fused2d_parity(const mcp_fused2d_plan* pl) { return pl ? pl->parity : 0; }
 
 int mcp_fused2d_set_parity(mcp_fused2d_plan* pl, int parity) {

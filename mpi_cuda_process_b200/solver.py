@@ -524,6 +524,26 @@ class Solver:
             stat = self._lib.mcp_fused3d_status if self.ndim == 3 else self._lib.mcp_fused2d_status
             _lib.check(stat(self._plan), "fused kernel status")
 
+    def verify_protocol(self) -> dict:
+        """Host-side check of the in-kernel flag protocol (2-D fused backend): after all ranks have finished their
+        runs, every halo counter must equal the number of arrivals the plan has accounted for -- a lost or duplicated
+        signal (or ranks that issued different run sequences) shows up here instead of as a silent hang later."""
+        if self.backend != "fused" or self.ndim != 2 or self._plan is None:
+            return {}
+        from .ops import _lib
+        torch.cuda.synchronize(self.ctx.device)
+        self.ctx.barrier()                      # neighbours' last pushes have been signalled
+        exp = (C.c_uint64 * 2)()
+        _lib.check(self._lib.mcp_fused2d_expected_flags(self._plan, exp))
+        got = self._arena.view(0, (2,), torch.int64).cpu().tolist()
+        up, dn = self.block.neighbors[0]
+        out = {"up": (got[0], int(exp[0])) if up is not None else None,
+               "down": (got[1], int(exp[1])) if dn is not None else None}
+        for k, v in out.items():
+            if v is not None and v[0] != v[1]:
+                raise RuntimeError(f"halo flag protocol violated on rank {self.ctx.rank} ({k}): counter {v[0]}, expected {v[1]}")
+        return out
+
     # -- plain kernel + exchange helpers ----------------------------------------------------------
     def _launch_plain(self, src: torch.Tensor, dst: torch.Tensor) -> None:
         from .ops import _lib

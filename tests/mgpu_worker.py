@@ -52,6 +52,7 @@ def main() -> int:
             s.initialize()
             st = s.run(g, residual=False)
             s.check_status()
+            s.verify_protocol()          # every halo counter equals the arrivals the plans accounted for
             got = s.gather()
             backend = s.backend
         if ctx.rank == 0:
