@@ -49,6 +49,7 @@ def parse_args(argv=None):
     p.add_argument("--chunk-rows", type=int, default=0)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--halo-message", default="row", choices=["row", "element"])
+    p.add_argument("--coarse-halo-flags", action="store_true", help="one arrival counter per neighbour instead of per-strip flags")
     return p.parse_args(argv)
 
 
@@ -102,7 +103,7 @@ def main(argv=None) -> int:
                     backend=backend,
                     decomposition=args.decomposition, seed=0 if args.workload == "life" else None,
                     time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
-                    extra={"chunk_rows": args.chunk_rows})
+                    extra={"chunk_rows": args.chunk_rows, "coarse_halo_flags": args.coarse_halo_flags})
     K, W = args.steps, max(args.warmup, 0)
 
     with Solver(cfg, ctx=ctx) as s:

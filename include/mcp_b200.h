@@ -29,6 +29,7 @@ extern "C" {
 
 #define MCP_MAX_RANKS 16
 #define MCP_RES_RING 64
+#define MCP_MAX_STRIPS 2048
 #define MCP_NORM_LINF 1
 #define MCP_NORM_L2 2
 
@@ -123,6 +124,13 @@ typedef struct mcp_fused2d_desc {
      * sum's association order is the switch's, so use the P2P variant when bit-identical sums across ranks matter. */
     void* nvls_local;
     void* nvls_mc;
+    /* Optional per-strip halo flags (finer than the two arrival counters): a zeroed array of 2 x MCP_MAX_STRIPS
+     * 64-bit words per rank ([0][s] written by rank-1, [1][s] by rank+1), and the addresses of the rows this rank
+     * writes: rank-1's [1][*] and rank+1's [0][*].  A boundary tile then waits only for the neighbour's boundary
+     * tiles of strips s-1, s, s+1 of the previous sweep. */
+    uint64_t* strip_flags;
+    uint64_t* up_strip_flag;
+    uint64_t* dn_strip_flag;
 } mcp_fused2d_desc;
 
 typedef struct mcp_fused2d_plan mcp_fused2d_plan;

@@ -39,6 +39,7 @@ class FusedDesc(C.Structure):
         ("res_inbox", C.c_void_p), ("res_flag", C.c_void_p),
         ("peer_res_inbox", C.c_void_p * 16), ("peer_res_flag", C.c_void_p * 16),
         ("nvls_local", C.c_void_p), ("nvls_mc", C.c_void_p),
+        ("strip_flags", C.c_void_p), ("up_strip_flag", C.c_void_p), ("dn_strip_flag", C.c_void_p),
     ]
 
 

@@ -58,12 +58,20 @@ __host__ __device__ constexpr int warps_for(int kind, int tb) {
 constexpr int kMaxResSlots = 16384;
 constexpr int kMaxRanks = MCP_MAX_RANKS;
 constexpr int kResRing = MCP_RES_RING;
+constexpr int kMaxStripFlags = MCP_MAX_STRIPS;
 
 struct Fused2dParams {
     void* buf[2];
     void* up_buf[2];
     void* dn_buf[2];
     const unsigned long long* my_flags;  // [0] arrivals from up, [1] arrivals from down
+    // per-strip halo flags (optional): [dir][strip] = number of sweeps whose boundary tile of that strip the neighbour
+    // has finished and pushed; a tile waits for strips s-1, s, s+1 only instead of for the neighbour's whole edge
+    const unsigned long long* strip_flags;
+    unsigned long long* up_strip_flag;  // up neighbour's [1][*] row (we are its down side)
+    unsigned long long* dn_strip_flag;  // down neighbour's [0][*] row
+    unsigned long long seq_base;        // sweeps completed by every rank before this launch
+    int prev_n_strips;                  // strip count of the previous launch (0 = none): sweep 0 waits for all of them
     unsigned long long* up_flag;
     unsigned long long* dn_flag;
     unsigned long long* grid_bar;
@@ -623,9 +631,25 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (c2 >= 0 && c2 < p.n_chunks && s2 >= 0 && s2 < p.n_strips)
                 wait_tile_done(p, &p.tile_done[encode_tile(c2, s2, p.n_strips, p.n_chunks)], (unsigned)sw);
         }
-        if (lane == 0) {
+        // Ghost rows this tile reads were written by the neighbour GPU during its previous sweep.
+        if (p.strip_flags != nullptr) {
+            const unsigned long long need = p.seq_base + (unsigned long long)sw;  // sweeps the neighbour must have done
+            if (need > 0) {
+                const bool regroup = (sw == 0 && p.prev_n_strips != p.n_strips);  // strips were cut differently
+#pragma unroll
+                for (int dir = 0; dir < 2; ++dir) {
+                    if ((dir == 0 ? up_out : dn_out) == nullptr) continue;
+                    const unsigned long long* row = p.strip_flags + dir * kMaxStripFlags;
+                    if (regroup) {
+                        for (int s2 = lane; s2 < p.prev_n_strips; s2 += 32) wait_counter_sys(p, &row[s2], need);
+                    } else if (lane < 3) {
+                        const int s2 = strip + lane - 1;
+                        if (s2 >= 0 && s2 < p.n_strips) wait_counter_sys(p, &row[s2], need);
+                    }
+                }
+            }
+        } else if (lane == 0) {
             bool ok = true;
-            // Ghost rows this tile reads were written by the neighbour GPU during its previous sweep.
             if (up_out != nullptr)
                 ok = wait_counter_sys(p, &p.my_flags[0], p.flag_base_up + (unsigned long long)sw * p.n_strips);
             if (ok && dn_out != nullptr)
@@ -659,12 +683,15 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&p.tile_done[q]), "r"((unsigned)(sw + 1))
                              : "memory");
             }
+            const unsigned long long done_seq = p.seq_base + (unsigned long long)sw + 1ull;
             if (up_out != nullptr) {
                 ptx::fence_acq_rel_sys();
+                if (p.up_strip_flag != nullptr) ptx::st_release_sys(&p.up_strip_flag[strip], done_seq);
                 ptx::red_add_release_sys(p.up_flag, 1ull);
             }
             if (dn_out != nullptr) {
                 ptx::fence_acq_rel_sys();
+                if (p.dn_strip_flag != nullptr) ptx::st_release_sys(&p.dn_strip_flag[strip], done_seq);
                 ptx::red_add_release_sys(p.dn_flag, 1ull);
             }
         }
@@ -826,6 +853,8 @@ struct mcp_fused2d_plan {
     int* stop_words;                // device: [0] stop word, [1] sweeps done
     unsigned* tile_done;            // device: [partials_cap_tiles]
     unsigned long long res_seq;     // sweeps whose residual has been exchanged so far
+    unsigned long long sweep_seq;   // sweeps completed so far (identical on every rank)
+    int last_ns;                    // strip count of the previous launch
     int last_generations;           // generations executed by the last run call
     std::vector<int> chunk_host[4];  // per time block 1,2,4,8
     unsigned long long flag_base_up, flag_base_dn, bar_base, ctr_base;
@@ -1000,6 +1029,11 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     }
     MCP_REQUIRE(!d.up_buf[0] || d.up_flag, "up_flag required with up_buf");
     MCP_REQUIRE(!d.dn_buf[0] || d.dn_flag, "dn_flag required with dn_buf");
+    if (d.strip_flags != nullptr) {
+        MCP_REQUIRE(!d.up_buf[0] || d.up_strip_flag, "up_strip_flag required with strip_flags and up_buf");
+        MCP_REQUIRE(!d.dn_buf[0] || d.dn_strip_flag, "dn_strip_flag required with strip_flags and dn_buf");
+        MCP_REQUIRE(ceil_div(d.w, outw_rt(d.dtype, 1)) <= kMaxStripFlags, "grid too wide for per-strip halo flags");
+    }
 
     mcp_fused2d_plan* pl = new (std::nothrow) mcp_fused2d_plan();
     MCP_REQUIRE(pl, "out of host memory");
@@ -1020,6 +1054,8 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->stop_words = nullptr;
     pl->tile_done = nullptr;
     pl->res_seq = 0;
+    pl->sweep_seq = 0;
+    pl->last_ns = 0;
     pl->last_generations = 0;
 
     int rc = device_sm_count(&pl->sm_count);
@@ -1167,6 +1203,11 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
                 p.peer_inbox[r] = (double*)d.peer_res_inbox[r];
                 p.peer_res_flag[r] = (unsigned long long*)d.peer_res_flag[r];
             }
+        p.strip_flags = (const unsigned long long*)d.strip_flags;
+        p.up_strip_flag = (unsigned long long*)d.up_strip_flag;
+        p.dn_strip_flag = (unsigned long long*)d.dn_strip_flag;
+        p.seq_base = pl->sweep_seq;
+        p.prev_n_strips = pl->last_ns;
         p.nvls_local = (unsigned char*)d.nvls_local;
         p.nvls_mc = (unsigned char*)d.nvls_mc;
         p.stop_word = pl->stop_words;
@@ -1208,6 +1249,8 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
         pl->flag_base_up += (unsigned long long)executed * ns;
         pl->flag_base_dn += (unsigned long long)executed * ns;
         pl->parity = (pl->parity + executed) & 1;
+        pl->sweep_seq += (unsigned long long)executed;
+        pl->last_ns = ns;
         if (res) {
             pl->res_slots_used = std::min(kMaxResSlots, pl->res_slots_used + executed);
             if (exchange) pl->res_seq += (unsigned long long)executed;

@@ -150,7 +150,7 @@ class Solver:
             self._buf_bytes = _round_up(max_alloc * self.pitch * self.esize, 4096)
             # signalling pad in front of the buffers: halo counters @0, residual arrival counter @256,
             # residual inbox ring (64 slots x 16 ranks x 16 B) @4096
-            self._flags_bytes = 32768
+            self._flags_bytes = 65536        # + per-strip halo flags (2 x 2048 x 8 B) @32768
             need_peers = self.backend == "fused" and self.ctx.distributed
             # halo pushes need the two neighbours; the fused residual all-reduce stores to every rank
             peers = list(range(self.ctx.world)) if need_peers else []
@@ -232,6 +232,10 @@ class Solver:
         d.flags = self._arena.peer_ptr(self.ctx.rank, 0)
         d.up_flag = self._arena.peer_ptr(up, 8) if up is not None else None      # up's flags[1]
         d.dn_flag = self._arena.peer_ptr(dn, 0) if dn is not None else None      # down's flags[0]
+        if self.ctx.distributed and not cfg.extra.get("coarse_halo_flags", False):
+            d.strip_flags = self._arena.peer_ptr(self.ctx.rank, 32768)
+            d.up_strip_flag = self._arena.peer_ptr(up, 32768 + 2048 * 8) if up is not None else None
+            d.dn_strip_flag = self._arena.peer_ptr(dn, 32768) if dn is not None else None
         d.ylo, d.yhi, d.xlo, d.xhi = self._fix_bounds
         d.chunk_rows = int(cfg.extra.get("chunk_rows", 0))
         d.max_ctas = int(cfg.extra.get("max_ctas", 0))
