@@ -1,0 +1,45 @@
+import json
+
+import numpy as np
+
+from mpi_cuda_process_b200 import models
+from mpi_cuda_process_b200.utils import metrics
+from mpi_cuda_process_b200.utils.clocks import ClockSampler, NvmlClockSampler
+
+
+def test_roofline_arithmetic():
+    peaks = {"hbm_gbs": 6400.0, "source": "measured"}
+    # 64 Mi cells, 8 B/update, 10 generations in 1 ms -> 5.4 TB/s effective
+    r = metrics.roofline(1 << 26, 10, 1.0, 8, 0.0, peaks)
+    assert r["bound"] == "hbm"
+    assert abs(r["effective_gbs"] - (1 << 26) * 8 * 10 / 1e-3 / 1e9) < 1e-6
+    assert abs(r["fraction_of_roofline"] - r["effective_gbs"] / 6400.0) < 1e-9
+    assert "of measured" in r["peaks_source"]
+    # a tiny grid with a huge halo is NVLink-bound
+    r2 = metrics.roofline(1024, 1, 1.0, 8, 1e9, peaks)
+    assert r2["bound"] == "nvlink"
+    assert metrics.glups(10**9, 2, 1000.0) == 2.0
+
+
+def test_measured_peaks_fallback(tmp_path):
+    assert metrics.measured_peaks(str(tmp_path))["source"] == "fallback"
+    (tmp_path / "MEASURED_PEAKS.json").write_text(json.dumps({"hbm_gbs": 6454.6}))
+    p = metrics.measured_peaks(str(tmp_path))
+    assert p["source"] == "measured" and p["hbm_gbs"] == 6454.6
+
+
+def test_clock_samplers_degrade_without_a_gpu():
+    for s in (ClockSampler(0), NvmlClockSampler(0)):
+        out = s.start().stop()
+        assert "reasons" in out and "samples" in out
+
+
+def test_workload_registry():
+    assert set(models.REGISTRY) == {"mdf", "life", "heat3d"}
+    m = models.get("mdf")
+    assert m.bytes_per_update("fp32") == 8 and m.bytes_per_update("fp64") == 16
+    u = m.step(m.init(6, 6))
+    assert u[1, 1] == np.float32(50.0)
+    import pytest
+    with pytest.raises(ValueError):
+        models.get("nope")
