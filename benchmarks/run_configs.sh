@@ -19,4 +19,4 @@ run --scaling weak --height 8192 --width 8192 --steps 2 --warmup 3 --gens-per-st
 # 5. fp64 32768^2 run-to-tolerance with the fused residual all-reduce (one launch)
 python -m torch.distributed.run --nnodes=1 --nproc-per-node="$N" --master-addr 127.0.0.1 --master-port 29542 \
     -m mpi_cuda_process_b200 --no-prompt --workload mdf --dtype fp64 --height 32768 --width 32768 \
-    --tol 0.02 --residual linf --max-generations 4000 --time-block 4 --json 2>/dev/null | grep '^{' | tee -a "$OUT"
+    --tol 0.005 --residual linf --max-generations 2000 --time-block 4 --json 2>/dev/null | grep '^{' | tee -a "$OUT"
