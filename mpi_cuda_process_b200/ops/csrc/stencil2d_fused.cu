@@ -53,6 +53,7 @@ __host__ __device__ constexpr int warps_for_tb(int tb) { return tb >= 8 ? kWarps
 // + horizontal sums, 24 per level), 2 = bit-packed Life (cells + two sum planes, 36 per level).  When the windows of
 // TB levels no longer fit 128 registers the CTA runs 8 warps x up to 255 registers instead of 16 x 128.
 __host__ __device__ constexpr int warps_for(int kind, int tb) {
+    if (kind == 2 && tb == 2) return 12;  // 148 registers: 12 warps x 32 x 148 fits the register file
     return (kind == 2 && tb >= 2) || (kind == 1 && tb >= 4) ? kWarpsTb8 : warps_for_tb(tb);
 }
 constexpr int kMaxResSlots = 16384;
