@@ -882,7 +882,7 @@ int outw_rt(int dtype, int tb) {
 
 int max_tb(int op, int dtype) {
     if (op == MCP_OP_LIFE) return 4;
-    return dtype == MCP_DTYPE_F64 ? 4 : 8;
+    return 8;
 }
 
 constexpr int kMaxChunks = 4096;
@@ -999,7 +999,10 @@ int launch_any(mcp_fused2d_plan* pl, int tb, const Fused2dParams& p, bool res, c
         if (tb == 8) return launch_variant<MdfF32, 8>(pl, p, res, stream);
         return launch_tb<MdfF32>(pl, tb, p, res, stream);
     }
-    if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F64) return launch_tb<MdfF64>(pl, tb, p, res, stream);
+    if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F64) {
+        if (tb == 8) return launch_variant<MdfF64, 8>(pl, p, res, stream);
+        return launch_tb<MdfF64>(pl, tb, p, res, stream);
+    }
     if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_I32) return launch_tb<LifeI32>(pl, tb, p, res, stream);
     if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_B1) return launch_tb<LifeB1>(pl, tb, p, res, stream);
     set_error("unsupported op/dtype combination %d/%d", d.op, d.dtype);

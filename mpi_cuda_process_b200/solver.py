@@ -72,7 +72,7 @@ class Solver:
         self.esize = 8 if cfg.dtype == "fp64" else 4
         # ghost depth: the fused kernel exchanges `time_block` rows every `time_block` generations
         if self.backend == "fused" and self.ndim == 2:
-            tbmax = 8 if (cfg.workload == "mdf" and cfg.dtype == "fp32") else 4
+            tbmax = 8 if cfg.workload == "mdf" else 4
             if self.bits:
                 tbmax = 2      # measured: 24.4 TLUPS at TB=2 vs 16.3 at TB=4 (36 window registers per level)
             tb = 1

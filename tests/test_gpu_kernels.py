@@ -96,7 +96,7 @@ def test_fused_mdf_random_field_many_chunks():
         assert s.gather().tobytes() == oracle.mdf_run(f, g).tobytes()
 
 
-@pytest.mark.parametrize("tb", [1, 2, 4])
+@pytest.mark.parametrize("tb", [1, 2, 4, 8])
 def test_fused_mdf_f64_bitwise(tb):
     h, w, g = 211, 390, 14
     cfg = RunConfig(workload="mdf", height=h, width=w, backend="fused", time_block=tb, dtype="fp64")
