@@ -23,6 +23,7 @@ CASES = [
     dict(workload="mdf", height=1037, width=2050, backend="fused", time_block=4, g=203),
     dict(workload="mdf", height=640, width=512, backend="fused", time_block=8, g=64),
     dict(workload="mdf", height=300, width=260, backend="fused", time_block=4, g=37, dtype="fp64"),
+    dict(workload="mdf", height=300, width=260, backend="fused", time_block=8, g=45, dtype="fp64", init="hash", seed=4),
     dict(workload="life", height=300, width=260, backend="fused", time_block=4, g=50),
     dict(workload="life", height=300, width=260, backend="fused", time_block=2, g=21, bc="fixed-ring"),
     dict(workload="life", dtype="bits", height=300, width=4500, backend="fused", time_block=4, g=50),
