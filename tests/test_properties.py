@@ -1,0 +1,89 @@
+"""Property-based checks (hypothesis) of the host-side logic: decomposition, oracle invariants, I/O round trips."""
+import numpy as np
+from hypothesis import given, settings, strategies as st
+
+from mpi_cuda_process_b200 import io as mio, oracle
+from mpi_cuda_process_b200.parallel.decomp import Decomposition, split_axis
+
+
+@settings(max_examples=60, deadline=None)
+@given(n=st.integers(1, 5000), parts=st.integers(1, 64))
+def test_split_axis_partition(n, parts):
+    if parts > n:
+        parts = n
+    r = split_axis(n, parts)
+    assert r[0][0] == 0 and r[-1][1] == n and len(r) == parts
+    assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+    sizes = [e - s for s, e in r]
+    assert max(sizes) - min(sizes) <= 1 and min(sizes) >= 1
+
+
+@settings(max_examples=40, deadline=None)
+@given(h=st.integers(8, 200), w=st.integers(3, 50), world=st.integers(1, 8))
+def test_slab_blocks_tile_the_grid_and_neighbours_are_mutual(h, w, world):
+    d = Decomposition.slab((h, w), world)
+    cover = np.zeros((h, w), dtype=np.int32)
+    for r in range(world):
+        b = d.block(r)
+        cover[d.global_slices(r)] += 1
+        lo, hi = b.neighbors[0]
+        if lo is not None:
+            assert d.block(lo).neighbors[0][1] == r and d.block(lo).stop[0] == b.start[0]
+        if hi is not None:
+            assert d.block(hi).neighbors[0][0] == r
+    assert (cover == 1).all()
+
+
+@settings(max_examples=25, deadline=None)
+@given(pz=st.integers(1, 4), py=st.integers(1, 4), d=st.integers(8, 40), h=st.integers(8, 40))
+def test_pencil_blocks_tile_the_grid(pz, py, d, h):
+    dec = Decomposition.pencil((d, h, 5), pz * py, (pz, py))
+    cover = np.zeros((d, h, 5), dtype=np.int32)
+    for r in range(pz * py):
+        cover[dec.global_slices(r)] += 1
+        assert dec.rank_of(dec.coords_of(r)) == r
+    assert (cover == 1).all()
+
+
+@settings(max_examples=25, deadline=None)
+@given(h=st.integers(3, 24), w=st.integers(3, 24), seed=st.integers(0, 10**6))
+def test_mdf_maximum_principle_and_fixed_ring(h, w, seed):
+    rng = np.random.default_rng(seed)
+    u = oracle.mdf_init(h, w)
+    u[1:-1, 1:-1] = rng.uniform(0, 100, (h - 2, w - 2)).astype(np.float32)
+    v = oracle.mdf_step(u)
+    assert (v[0] == u[0]).all() and (v[-1] == u[-1]).all() and (v[:, 0] == u[:, 0]).all() and (v[:, -1] == u[:, -1]).all()
+    # a convex combination of the four neighbours (up to rounding): stays inside the data range
+    assert v.min() >= u.min() - 1e-3 and v.max() <= u.max() + 1e-3
+
+
+@settings(max_examples=25, deadline=None)
+@given(h=st.integers(1, 20), w=st.integers(1, 20), seed=st.integers(0, 10**6))
+def test_life_matches_bruteforce_and_print_array_roundtrip(h, w, seed):
+    rng = np.random.default_rng(seed)
+    u = (rng.random((h, w)) < 0.45).astype(np.int32)
+    v = oracle.life_step(u)
+    for i in range(h):
+        for j in range(w):
+            n = sum(u[y, x] for y in range(max(0, i - 1), min(h, i + 2)) for x in range(max(0, j - 1), min(w, j + 2))) - u[i, j]
+            assert v[i, j] == (1 if (n == 3 or (n == 2 and u[i, j])) else 0)
+    assert (mio.parse_array(mio.format_array(u), w) == u).all()
+
+
+@settings(max_examples=30, deadline=None)
+@given(rows=st.integers(1, 6), w=st.integers(1, 300), seed=st.integers(0, 10**6))
+def test_bit_packing_roundtrip(rows, w, seed):
+    from mpi_cuda_process_b200.solver import Solver
+
+    class Shim:
+        pass
+    f = Shim()
+    f.cfg = Shim()
+    f.cfg.width = w
+    f.pitch = ((w + 31) // 32 + 31) // 32 * 32
+    cells = (np.random.default_rng(seed).random((rows, w)) < 0.5).astype(np.int32)
+    words = Solver._pack_bits(f, cells)
+    assert words.shape == (rows, f.pitch)
+    assert (Solver._unpack_bits(f, words) == cells).all()
+    x = int(np.random.default_rng(seed + 1).integers(0, w))
+    assert ((int(words[0, x // 32]) >> (x % 32)) & 1) == cells[0, x]
