@@ -145,6 +145,10 @@ int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int
  * generation count only (M:153,157,186). */
 int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* plan, int max_generations, int time_block, int norm, double tol,
                                  int* generations_done, void* stream);
+/* Tile trace (set MCP_DEBUG_FLAGS=4 before creating the plan): duration in ns of every tile of the last sweep, in
+ * queue order, with its chunk and strip index.  Returns the number of entries. */
+int mcp_fused2d_tile_trace(mcp_fused2d_plan* plan, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
+                           int max_entries);
 /* Protocol check: the number of halo arrivals this rank should have received so far from rank-1 and rank+1.
  * After a synchronised run the local counters flags[0], flags[1] must equal these (when that neighbour exists). */
 int mcp_fused2d_expected_flags(const mcp_fused2d_plan* plan, uint64_t* up_dn);

@@ -93,6 +93,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_create.argtypes = [C.POINTER(FusedDesc), c_void_pp]
     lib.mcp_fused2d_run.argtypes = [vp, i, i, i, vp]
     lib.mcp_fused2d_run_to_tolerance.argtypes = [vp, i, i, i, dbl, C.POINTER(i), vp]
+    lib.mcp_fused2d_tile_trace.argtypes = [vp, i, vp, vp, vp, i]
     lib.mcp_fused2d_expected_flags.argtypes = [vp, vp]
     lib.mcp_fused2d_parity.argtypes = [vp]
     lib.mcp_fused2d_set_parity.argtypes = [vp, i]

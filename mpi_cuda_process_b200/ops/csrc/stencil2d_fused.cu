@@ -78,6 +78,7 @@ struct Fused2dParams {
     unsigned long long* grid_bar;
     unsigned long long* tile_ctr;
     unsigned* tile_done;  // [n_tiles] last sweep (1-based, within this launch) each tile has completed
+    unsigned* tile_ns;    // [n_tiles] trace (debug_flags & 4): duration of the tile in the last sweep it ran, in ns
     int* status;
     double* partials;  // [2][n_tiles][2]
     double* res_out;   // [kMaxResSlots][2]
@@ -662,7 +663,10 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (aborted(p)) return;
 
         double rs = 0.0, rm = 0.0;
+        const bool trace = (p.debug_flags & 4) != 0;
+        const unsigned long long t_begin = trace ? ptx::globaltimer_ns() : 0ull;
         process_tile<Op, TB, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
+        if (trace && lane == 0) p.tile_ns[q] = (unsigned)(ptx::globaltimer_ns() - t_begin);
 
         if (RES) {
 #pragma unroll
@@ -853,6 +857,8 @@ struct mcp_fused2d_plan {
     int* chunk_tab;                 // device: kNumTb tables of kMaxChunks + 1 row boundaries
     int* stop_words;                // device: [0] stop word, [1] sweeps done
     unsigned* tile_done;            // device: [partials_cap_tiles]
+    unsigned* tile_ns;              // device: [partials_cap_tiles] per-tile trace
+    int last_tiles;                 // tile count of the last launch
     unsigned long long res_seq;     // sweeps whose residual has been exchanged so far
     unsigned long long sweep_seq;   // sweeps completed so far (identical on every rank)
     int last_ns;                    // strip count of the previous launch
@@ -1057,6 +1063,8 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->chunk_tab = nullptr;
     pl->stop_words = nullptr;
     pl->tile_done = nullptr;
+    pl->tile_ns = nullptr;
+    pl->last_tiles = 0;
     pl->res_seq = 0;
     pl->sweep_seq = 0;
     pl->last_ns = 0;
@@ -1096,7 +1104,9 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         mcp_fused2d_destroy(pl);
         return MCP_ERR_CUDA;
     }
-    if ((e = cudaMalloc(&pl->tile_done, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess) {
+    if ((e = cudaMalloc(&pl->tile_ns, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
+        (e = cudaMemset(pl->tile_ns, 0, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
+        (e = cudaMalloc(&pl->tile_done, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess) {
         set_error("mcp_fused2d_create: tile flag allocation failed: %s", cudaGetErrorString(e));
         mcp_fused2d_destroy(pl);
         return MCP_ERR_CUDA;
@@ -1174,6 +1184,8 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool 
         p.tile_ctr = pl->grid_bar + 16;  // separate 128-byte line of the same zeroed allocation
         p.ctr_base = pl->ctr_base;
         p.tile_done = pl->tile_done;
+        p.tile_ns = pl->tile_ns;
+        pl->last_tiles = ns * nc;
         p.status = pl->status;
         p.partials = pl->partials;
         p.res_out = pl->res_out;
@@ -1286,6 +1298,23 @@ int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int 
     return rc;
 }
 
+// Trace (MCP_DEBUG_FLAGS & 4): duration in ns of every tile in the last sweep it ran, in queue order, with its
+// (chunk, strip) so that a host tool can see which tiles are the critical path.
+int mcp_fused2d_tile_trace(mcp_fused2d_plan* pl, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
+                           int max_entries) {
+    MCP_REQUIRE(pl && ns_out, "null argument");
+    int nstr, nch;
+    choose_geometry(pl, time_block, &nstr, &nch);
+    const int n = std::min(std::min(nstr * nch, pl->last_tiles), max_entries);
+    if (n > 0) MCP_CUDA_TRY(cudaMemcpy(ns_out, pl->tile_ns, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    for (int q = 0; q < n; ++q) {
+        const int ci = q / nstr;
+        if (strip_out) strip_out[q] = q - ci * nstr;
+        if (chunk_out) chunk_out[q] = (ci & 1) ? nch - 1 - (ci >> 1) : (ci >> 1);
+    }
+    return n;
+}
+
 int mcp_fused2d_expected_flags(const mcp_fused2d_plan* pl, uint64_t* up_dn) {
     MCP_REQUIRE(pl && up_dn, "null argument");
     up_dn[0] = pl->flag_base_up;
@@ -1333,6 +1362,7 @@ int mcp_fused2d_destroy(mcp_fused2d_plan* pl) {
     if (pl->chunk_tab) cudaFree(pl->chunk_tab);
     if (pl->stop_words) cudaFree(pl->stop_words);
     if (pl->tile_done) cudaFree(pl->tile_done);
+    if (pl->tile_ns) cudaFree(pl->tile_ns);
     delete pl;
     return MCP_OK;
 }
