@@ -7,8 +7,6 @@ import fails loudly instead of falling back to PyTorch ops.  On a CPU-only box o
 from __future__ import annotations
 
 import ctypes as C
-import os
-from pathlib import Path
 from typing import Optional
 
 from . import build as _build
