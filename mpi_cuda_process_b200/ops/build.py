@@ -129,8 +129,23 @@ def build_host(force: bool = False, verbose: bool = False) -> Path:
     if not force and out.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
         return out
     cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
-    _run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off",
-          *[str(CSRC / n) for n in HOST_SOURCES], "-o", str(out)], verbose)
+    base = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", *[str(CSRC / n) for n in HOST_SOURCES],
+            "-o", str(out)]
+    # OpenMP where the toolchain has it (some g++ installs ship without libgomp): rows are independent, results are
+    # bit-identical either way
+    attempts = [[cxx, "-fopenmp", *base], [cxx, *base]]
+    if shutil.which("g++") and shutil.which("g++") != cxx:
+        attempts.insert(1, [shutil.which("g++"), "-fopenmp", *base])
+    err = None
+    for cmd in attempts:
+        try:
+            _run(cmd, verbose)
+            err = None
+            break
+        except RuntimeError as e:
+            err = e
+    if err is not None:
+        raise err
     stamp_file.write_text(stamp)
     return out
 

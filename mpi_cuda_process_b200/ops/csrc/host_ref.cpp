@@ -27,6 +27,7 @@ int mcp_host_life_init_reference(int32_t* u, int h, int w, float prob) {
 
 int mcp_host_mdf_step_f32(const float* in, float* out, int h, int w, int strict_fp64) {
     memcpy(out, in, (size_t)h * w * sizeof(float));
+#pragma omp parallel for schedule(static)
     for (int i = 1; i < h - 1; ++i)
         for (int j = 1; j < w - 1; ++j) {
             const int64_t k = (int64_t)i * w + j;
@@ -42,6 +43,7 @@ int mcp_host_mdf_step_f32(const float* in, float* out, int h, int w, int strict_
 
 int mcp_host_mdf_step_f64(const double* in, double* out, int h, int w) {
     memcpy(out, in, (size_t)h * w * sizeof(double));
+#pragma omp parallel for schedule(static)
     for (int i = 1; i < h - 1; ++i)
         for (int j = 1; j < w - 1; ++j) {
             const int64_t k = (int64_t)i * w + j;
@@ -56,6 +58,7 @@ int mcp_host_mdf_step_f64(const double* in, double* out, int h, int w) {
 }
 
 int mcp_host_life_step(const int32_t* in, int32_t* out, int h, int w, int fixed_ring) {
+#pragma omp parallel for schedule(static)
     for (int i = 0; i < h; ++i)
         for (int j = 0; j < w; ++j) {
             const int64_t k = (int64_t)i * w + j;
