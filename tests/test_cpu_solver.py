@@ -80,14 +80,6 @@ def test_life_glider_crosses_the_cut(bc):
     h, w = 24, 16
     u = np.zeros((h, w), dtype=np.int32)
     u[8:11, 5:8] = np.array([[0, 1, 0], [0, 0, 1], [1, 1, 1]])   # glider heading down-right across row 12
-    def run(rank, world, field, bc):
-        from mpi_cuda_process_b200.config import RunConfig
-        from mpi_cuda_process_b200.solver import Solver
-        cfg = RunConfig(workload="life", height=24, width=16, backend="cpu", bc=bc)
-        with Solver(cfg) as s:
-            s.initialize(field)
-            s.run(20)
-            return s.gather()
     res = run_ranks(_glider_worker, 2, u, bc)
     assert (res[0] == oracle.life_run(u, 20, bc)).all()
     assert res[0][12:].sum() > 0
