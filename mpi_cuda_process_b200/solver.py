@@ -724,7 +724,8 @@ class Solver:
         tol = self.cfg.tol if tol is None else tol
         if tol is None:
             raise ValueError("no tolerance given")
-        max_g = max_generations or self.cfg.max_generations or self.cfg.generations or 1 << 30
+        max_g = (max_generations or self.cfg.max_generations
+                 or (self.cfg.generations if self.cfg.generations > 1 else 100000))   # 1 = "not given"
         every = check_every or self.cfg.check_every or max(self.time_block, 1) * 25
         if self.backend == "fused":
             every = max(self.time_block, every // self.time_block * self.time_block)
