@@ -145,6 +145,10 @@ int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int
  * generation count only (M:153,157,186). */
 int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* plan, int max_generations, int time_block, int norm, double tol,
                                  int* generations_done, void* stream);
+/* Device-free planning (pure host arithmetic, works without a GPU): chunk heights in queue order and strip count
+ * that a plan would use for a slab of rows_own x w cells on `grid` CTAs.  Returns the chunk count. */
+int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
+                              int chunk_rows, int* rows_out, int max_entries, int* n_strips);
 /* Tile trace (set MCP_DEBUG_FLAGS=4 before creating the plan): duration in ns of every tile of the last sweep, in
  * queue order, with its chunk and strip index.  Returns the number of entries. */
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* plan, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,

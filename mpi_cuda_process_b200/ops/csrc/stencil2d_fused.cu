@@ -1298,6 +1298,31 @@ int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int 
     return rc;
 }
 
+// Device-free planning: the tile schedule a plan WOULD use (chunk heights in queue order, strip count) for a slab of
+// `rows_own` rows and `w` cells on `grid` CTAs.  Pure host arithmetic -- usable on a box without a GPU (tests).
+int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
+                              int chunk_rows, int* rows_out, int max_entries, int* n_strips) {
+    MCP_REQUIRE(rows_out && n_strips, "null argument");
+    MCP_REQUIRE(w >= 1 && rows_own >= 1 && ghost >= 1 && grid >= 1, "bad geometry");
+    MCP_REQUIRE(time_block == 1 || time_block == 2 || time_block == 4 || time_block == 8, "time_block must be 1, 2, 4 or 8");
+    mcp_fused2d_plan tmp;
+    memset(&tmp.d, 0, sizeof(tmp.d));
+    tmp.d.op = op;
+    tmp.d.dtype = dtype;
+    tmp.d.w = w;
+    tmp.d.rows_own = rows_own;
+    tmp.d.ghost = ghost;
+    tmp.d.chunk_rows = chunk_rows;
+    tmp.grid = grid;
+    std::vector<int> y;
+    int ns = 0;
+    build_chunks(&tmp, time_block, &y, &ns);
+    *n_strips = ns;
+    const int n = std::min((int)y.size() - 1, max_entries);
+    for (int i = 0; i < n; ++i) rows_out[i] = y[i + 1] - y[i];
+    return (int)y.size() - 1;
+}
+
 // Trace (MCP_DEBUG_FLAGS & 4): duration in ns of every tile in the last sweep it ran, in queue order, with its
 // (chunk, strip) so that a host tool can see which tiles are the critical path.
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* pl, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,

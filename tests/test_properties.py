@@ -87,3 +87,30 @@ def test_bit_packing_roundtrip(rows, w, seed):
     assert (Solver._unpack_bits(f, words) == cells).all()
     x = int(np.random.default_rng(seed + 1).integers(0, w))
     assert ((int(words[0, x // 32]) >> (x % 32)) & 1) == cells[0, x]
+
+
+@settings(max_examples=80, deadline=None)
+@given(rows=st.integers(1, 40000), w=st.integers(1, 40000), tb=st.sampled_from([1, 2, 4, 8]),
+       dtype=st.sampled_from([0, 1, 2, 3]), grid=st.sampled_from([1, 37, 148]), chunk_rows=st.sampled_from([0, 0, 7, 48, 500]))
+def test_tile_schedule_invariants_without_a_gpu(rows, w, tb, dtype, grid, chunk_rows):
+    """The fused kernel's host-side planning (pure arithmetic in the native library) for arbitrary slabs."""
+    import ctypes as C
+    from mpi_cuda_process_b200.ops import _lib
+    lib = _lib.cuda_lib()                       # loads without a GPU; only host code is called
+    op = 1 if dtype in (2, 3) else 0
+    if op == 1 and tb == 8:
+        tb = 4
+    ghost = tb
+    if rows < ghost:
+        rows = ghost
+    out = (C.c_int * 8192)()
+    ns = C.c_int(0)
+    n = lib.mcp_fused2d_plan_schedule(op, dtype, w, rows, ghost, tb, grid, chunk_rows, out, 8192, C.byref(ns))
+    assert 1 <= n <= 4096
+    hts = [out[i] for i in range(n)]
+    assert sum(hts) == rows                                  # the chunks tile the slab exactly
+    assert min(hts) >= min(ghost, rows)                      # every chunk holds the halo rows a neighbour needs
+    cells_per_lane = {0: 4, 1: 2, 2: 4, 3: 128}[dtype]
+    margin = -(-tb // cells_per_lane)
+    outw = (32 - 2 * margin) * cells_per_lane
+    assert ns.value == -(-w // outw) and ns.value <= 2048 or w > 2048 * outw
