@@ -145,6 +145,8 @@ int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int
  * generation count only (M:153,157,186). */
 int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* plan, int max_generations, int time_block, int norm, double tol,
                                  int* generations_done, void* stream);
+/* Queue position q -> (chunk, strip) of the sweep's tile order; returns the position computed back from them. */
+int mcp_fused2d_tile_at(int n_strips, int n_chunks, int q, int* chunk, int* strip);
 /* Device-free planning (pure host arithmetic, works without a GPU): chunk heights in queue order and strip count
  * that a plan would use for a slab of rows_own x w cells on `grid` CTAs.  Returns the chunk count. */
 int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,

@@ -91,6 +91,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_create.argtypes = [C.POINTER(FusedDesc), c_void_pp]
     lib.mcp_fused2d_run.argtypes = [vp, i, i, i, vp]
     lib.mcp_fused2d_run_to_tolerance.argtypes = [vp, i, i, i, dbl, C.POINTER(i), vp]
+    lib.mcp_fused2d_tile_at.argtypes = [i, i, i, C.POINTER(i), C.POINTER(i)]
     lib.mcp_fused2d_plan_schedule.argtypes = [i, i, i, i, i, i, i, i, vp, i, C.POINTER(i)]
     lib.mcp_fused2d_tile_trace.argtypes = [vp, i, vp, vp, vp, i]
     lib.mcp_fused2d_expected_flags.argtypes = [vp, vp]

@@ -549,14 +549,14 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
 // The slab-cut chunks come first so their halo pushes overlap the rest of the sweep, and a chunk's neighbours in
 // the previous sweep were finished equally early, so the barrier-free path never has an early ticket waiting for
 // a late one.
-__device__ __forceinline__ void decode_tile(int q, int ns, int nc, int& chunk, int& strip) {
+__host__ __device__ __forceinline__ void decode_tile(int q, int ns, int nc, int& chunk, int& strip) {
     const int ci = q / ns;
     strip = q - ci * ns;
     chunk = (ci & 1) ? nc - 1 - (ci >> 1) : (ci >> 1);
 }
 
 // Inverse of decode_tile.
-__device__ __forceinline__ int encode_tile(int chunk, int strip, int ns, int nc) {
+__host__ __device__ __forceinline__ int encode_tile(int chunk, int strip, int ns, int nc) {
     const int ci = (chunk <= nc - 1 - chunk) ? 2 * chunk : 2 * (nc - 1 - chunk) + 1;
     return ci * ns + strip;
 }
@@ -1296,6 +1296,13 @@ int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int 
                       (cudaStream_t)stream_);
     if (generations_done) *generations_done = pl->last_generations;
     return rc;
+}
+
+// Queue position <-> (chunk, strip), the same functions the kernel uses (host build of decode_tile/encode_tile).
+int mcp_fused2d_tile_at(int n_strips, int n_chunks, int q, int* chunk, int* strip) {
+    MCP_REQUIRE(chunk && strip && n_strips >= 1 && n_chunks >= 1 && q >= 0 && q < n_strips * n_chunks, "bad arguments");
+    decode_tile(q, n_strips, n_chunks, *chunk, *strip);
+    return encode_tile(*chunk, *strip, n_strips, n_chunks);
 }
 
 // Device-free planning: the tile schedule a plan WOULD use (chunk heights in queue order, strip count) for a slab of

@@ -114,3 +114,26 @@ def test_tile_schedule_invariants_without_a_gpu(rows, w, tb, dtype, grid, chunk_
     margin = -(-tb // cells_per_lane)
     outw = (32 - 2 * margin) * cells_per_lane
     assert ns.value == -(-w // outw) and ns.value <= 2048 or w > 2048 * outw
+
+
+@settings(max_examples=40, deadline=None)
+@given(ns=st.integers(1, 40), nc=st.integers(1, 40))
+def test_tile_order_is_a_bijection_and_runs_outside_in(ns, nc):
+    """The barrier-free sweeps rely on this order: positions map one-to-one to tiles, slab-cut chunks come first,
+    and the chunks a tile depends on (c-1, c, c+1) sit at most two chunk-groups away in the queue."""
+    import ctypes as C
+    from mpi_cuda_process_b200.ops import _lib
+    lib = _lib.cuda_lib()
+    seen = set()
+    pos_of_chunk = {}
+    for q in range(ns * nc):
+        c, s_ = C.c_int(), C.c_int()
+        back = lib.mcp_fused2d_tile_at(ns, nc, q, C.byref(c), C.byref(s_))
+        assert back == q
+        assert 0 <= c.value < nc and 0 <= s_.value < ns
+        seen.add((c.value, s_.value))
+        pos_of_chunk.setdefault(c.value, q // ns)
+    assert len(seen) == ns * nc
+    assert pos_of_chunk[0] == 0 and (nc == 1 or pos_of_chunk[nc - 1] == 1)
+    for c in range(nc - 1):
+        assert abs(pos_of_chunk[c] - pos_of_chunk[c + 1]) <= 2
