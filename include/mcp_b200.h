@@ -52,6 +52,11 @@ int mcp_ipc_get_handle(void* ptr, void* handle_out);
 int mcp_ipc_open_handle(const void* handle, void** ptr_out);
 int mcp_ipc_close_handle(void* ptr);
 int mcp_enable_peer_access(int peer_device);
+/* Conveniences for hosts that do not link the CUDA runtime themselves (see examples/solve_mdf.c). */
+int mcp_set_device(int device);
+int mcp_device_synchronize(void);
+int mcp_copy_to_host(void* dst_host, const void* src_dev, size_t bytes);
+int mcp_copy_to_device(void* dst_dev, const void* src_host, size_t bytes);
 
 /* ---- initialisation and boundary conditions (reference: create_universe, M:88-99, K:131-146) --- */
 /* Fill local rows [0, rows_alloc) of a pitched buffer from the global init rule: global row of local

@@ -127,6 +127,29 @@ int mcp_ipc_close_handle(void* ptr) {
     return MCP_OK;
 }
 
+// Small conveniences for hosts that do not link the CUDA runtime themselves (pure C, ctypes, ...).
+int mcp_copy_to_host(void* dst_host, const void* src_dev, size_t bytes) {
+    MCP_REQUIRE(dst_host && src_dev, "mcp_copy_to_host: null argument");
+    MCP_CUDA_TRY(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+    return MCP_OK;
+}
+
+int mcp_copy_to_device(void* dst_dev, const void* src_host, size_t bytes) {
+    MCP_REQUIRE(dst_dev && src_host, "mcp_copy_to_device: null argument");
+    MCP_CUDA_TRY(cudaMemcpy(dst_dev, src_host, bytes, cudaMemcpyHostToDevice));
+    return MCP_OK;
+}
+
+int mcp_device_synchronize(void) {
+    MCP_CUDA_TRY(cudaDeviceSynchronize());
+    return MCP_OK;
+}
+
+int mcp_set_device(int device) {
+    MCP_CUDA_TRY(cudaSetDevice(device));
+    return MCP_OK;
+}
+
 // Same-process peer mapping (used by single-process multi-GPU tests and tools).
 int mcp_enable_peer_access(int peer_device) {
     int dev = 0, can = 0;
