@@ -2,6 +2,9 @@
  * The launcher exports MCP_MPI_RANK, MCP_MPI_SIZE and MCP_MPI_DIR; pipe "<dir>/p_<src>_<dst>" carries the messages
  * from src to dst as (tag, nbytes, payload) records.  A send blocks once the pipe buffer is full (like an MPI
  * rendezvous), a receive blocks until the next record arrives; records of one pair are delivered in order. */
+#ifndef _GNU_SOURCE
+#define _GNU_SOURCE /* F_SETPIPE_SZ */
+#endif
 #include "mpi.h"
 
 #include <errno.h>
@@ -78,6 +81,12 @@ int MPI_Init(int* argc, char*** argv) {
         g_out[p] = open_pipe(g_rank, p, O_RDWR);
         g_in[p] = open_pipe(p, g_rank, O_RDWR);
         if (g_out[p] < 0 || g_in[p] < 0) return MPI_ERR_OTHER;
+#ifdef F_SETPIPE_SZ
+        /* "eager buffer": a border row of one-element messages (12 B each) must fit without a matching receive,
+         * as it would in a real MPI's eager protocol (the reference sends at the end of a generation and receives
+         * at the start of the next one, MDF_kernel.cu:166-183).  Best effort; the default is 64 KiB. */
+        (void)fcntl(g_out[p], F_SETPIPE_SZ, 1 << 20);
+#endif
     }
     g_init = 1;
     return MPI_SUCCESS;

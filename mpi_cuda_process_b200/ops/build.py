@@ -9,6 +9,8 @@ shared objects are built next to the sources so that they travel with the tree.
 """
 from __future__ import annotations
 
+import contextlib
+import fcntl
 import hashlib
 import os
 import shutil
@@ -68,6 +70,19 @@ def host_lib_path() -> Path:
     return LIBDIR / "libmcp_host.so"
 
 
+@contextlib.contextmanager
+def _build_lock():
+    """One builder at a time per tree: under torchrun every rank imports the package at once, and a rank must
+    never load a half-written shared object (outputs are linked under a temporary name and renamed)."""
+    LIBDIR.mkdir(exist_ok=True)
+    with open(LIBDIR / ".build.lock", "w") as f:
+        fcntl.flock(f, fcntl.LOCK_EX)
+        try:
+            yield
+        finally:
+            fcntl.flock(f, fcntl.LOCK_UN)
+
+
 def _run(cmd, verbose):
     if verbose:
         print("+", " ".join(str(c) for c in cmd), flush=True)
@@ -85,13 +100,21 @@ def _obj_stale(src: Path, obj: Path, stamp: str) -> bool:
 
 
 def build_cuda(force: bool = False, verbose: bool = False, ptxas_info: bool = False) -> Path:
-    LIBDIR.mkdir(exist_ok=True)
-    OBJDIR.mkdir(exist_ok=True)
+    """Build (or confirm up to date) libmcp_b200.so.  Cheap when nothing changed: one hash over the sources."""
     out = lib_path()
     stamp_all = _sources_hash(CUDA_SOURCES)
     stamp_file = LIBDIR / "libmcp_b200.hash"
     if not force and out.exists() and stamp_file.exists() and stamp_file.read_text() == stamp_all:
         return out
+    with _build_lock():
+        if not force and out.exists() and stamp_file.exists() and stamp_file.read_text() == stamp_all:
+            return out          # another process built it while we waited for the lock
+        return _build_cuda_locked(out, stamp_all, stamp_file, force, verbose, ptxas_info)
+
+
+def _build_cuda_locked(out: Path, stamp_all: str, stamp_file: Path, force: bool, verbose: bool,
+                       ptxas_info: bool) -> Path:
+    OBJDIR.mkdir(exist_ok=True)
     nvcc = _nvcc()
     headers_stamp = hashlib.sha256(
         b"".join(p.read_bytes() for p in sorted(CSRC.glob("*.cuh")) + sorted(INCLUDE.glob("*.h")))
@@ -115,19 +138,29 @@ def build_cuda(force: bool = False, verbose: bool = False, ptxas_info: bool = Fa
 
     with ThreadPoolExecutor(max_workers=min(8, len(CUDA_SOURCES))) as ex:
         objs = list(ex.map(compile_one, CUDA_SOURCES))
-    _run([nvcc, "-shared", "-o", str(out), *[str(o) for o in objs], "-gencode", "arch=compute_100a,code=sm_100a",
+    tmp = out.with_suffix(f".so.tmp{os.getpid()}")
+    _run([nvcc, "-shared", "-o", str(tmp), *[str(o) for o in objs], "-gencode", "arch=compute_100a,code=sm_100a",
           "-Xcompiler", "-fPIC"], verbose)
+    os.replace(tmp, out)
     stamp_file.write_text(stamp_all)
     return out
 
 
 def build_host(force: bool = False, verbose: bool = False) -> Path:
-    LIBDIR.mkdir(exist_ok=True)
     out = host_lib_path()
     stamp = _sources_hash(HOST_SOURCES)
     stamp_file = LIBDIR / "libmcp_host.hash"
     if not force and out.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
         return out
+    with _build_lock():
+        if not force and out.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
+            return out
+        return _build_host_locked(out, stamp, stamp_file, verbose)
+
+
+def _build_host_locked(out: Path, stamp: str, stamp_file: Path, verbose: bool) -> Path:
+    final = out
+    out = final.with_suffix(f".so.tmp{os.getpid()}")
     cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
     base = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", *[str(CSRC / n) for n in HOST_SOURCES],
             "-o", str(out)]
@@ -146,8 +179,9 @@ def build_host(force: bool = False, verbose: bool = False) -> Path:
             err = e
     if err is not None:
         raise err
+    os.replace(out, final)
     stamp_file.write_text(stamp)
-    return out
+    return final
 
 
 def build_all(force: bool = False, verbose: bool = False, ptxas_info: bool = False):
