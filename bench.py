@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """Headline benchmark: grid-point updates per second (GLUPS) of the 2-D 5-point MDF solve.
 
-Config (BASELINE.json #2): 16384 x 16384 fp32, 1-D slab decomposition over N GPUs of one box, fixed
-1000 iterations = ``--steps 10`` steps of 100 generations.  Strong scaling: the global grid is fixed.
+Config (BASELINE.json #2): 16384 x 16384 fp32, 1-D slab decomposition over N GPUs of one box.  One step = one
+complete solve of the configured 1000 iterations (``--gens-per-step 1000``, ONE kernel launch per rank); ``--steps K``
+repeats that solve K times, so a run executes K x 1000 iterations and GLUPS is their rate.  Strong scaling: the global
+grid is fixed.
 
     python bench.py --gpus 1 --steps 10 --warmup 3
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
@@ -10,7 +12,9 @@ Config (BASELINE.json #2): 16384 x 16384 fp32, 1-D slab decomposition over N GPU
 
 Rank 0 prints ONE JSON line.  ``value`` is device-timed (CUDA events around the K steps, max over ranks);
 ``e2e`` repeats the measurement through the public API with a pinned-host -> device upload of the rank's slab
-and a device -> host read of the residual inside every step.
+and a device -> host read of the step's result (kernel status + global residual of the last iteration) inside every
+step; ``e2e_with_gather`` additionally assembles the solution field on rank 0 (fused gather + pack over NVLink) and
+copies it to pinned host memory every step.
 ``--impl reference`` is the reference arm (the reference cannot be built or run here).
 """
 from __future__ import annotations
@@ -46,7 +50,8 @@ def parse_args(argv=None):
     p.add_argument("--dtype", default="fp32", choices=["fp32", "fp64", "bits"])
     p.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                    help="weak: --height is per GPU (BASELINE.json config 4 uses 8192 x 8192 per GPU)")
-    p.add_argument("--chunk-rows", type=int, default=0)
+    p.add_argument("--chunk-rows", type=int, default=0, help="rows per tile of the schedule (0 = default)")
+    p.add_argument("--sync-mode", type=int, default=None, help="1 = grid barrier between sweeps, 2 = dataflow flags")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--halo-message", default="row", choices=["row", "element"])
     p.add_argument("--coarse-halo-flags", action="store_true", help="one arrival counter per neighbour instead of per-strip flags")
@@ -103,7 +108,8 @@ def main(argv=None) -> int:
                     backend=backend,
                     decomposition=args.decomposition, seed=0 if args.workload == "life" else None,
                     time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
-                    extra={"chunk_rows": args.chunk_rows, "coarse_halo_flags": args.coarse_halo_flags})
+                    extra={"chunk_rows": args.chunk_rows, "sync_mode": args.sync_mode,
+                           "coarse_halo_flags": args.coarse_halo_flags})
     K, W = args.steps, max(args.warmup, 0)
 
     with Solver(cfg, ctx=ctx) as s:
@@ -141,14 +147,14 @@ def main(argv=None) -> int:
                     "chunk_rows_first_max_last": [crow[0], max(crow), crow[-1]] if crow else None}
 
         # ---------------- end to end through the public API ----------------
-        e2e = None
+        e2e = e2e_gather = None
         if not args.no_e2e:
             host = torch.empty(s.store_shape, dtype=s.tdtype).pin_memory()
             host.copy_(s.bufs[s.cur])                     # a valid slab (incl. ghost rows) to upload every step
             torch.cuda.synchronize()
             h2d = host.numel() * host.element_size()
             tb = s.time_block
-            d2h = 16 + 4                                   # (sum of squares, max) of the last generation + status word
+            d2h = 32                                       # result block: status, sweeps done, (sum of squares, max)
 
             def one_step():
                 s.commit_input()                          # this step's input (uploaded while the previous step ran)
@@ -163,6 +169,7 @@ def main(argv=None) -> int:
             ctx.barrier()
             t0 = time.perf_counter()
             last = None
+            l0 = s.total_stats.launches
             for _ in range(K):
                 last = one_step()
             torch.cuda.synchronize()                      # includes the upload issued in the last step
@@ -170,13 +177,37 @@ def main(argv=None) -> int:
             e2e_ms = ctx.all_reduce_max((t1 - t0) * 1e3)
             e2e = {"value": round(cells * gps * K / (e2e_ms * 1e-3) / 1e9, 3), "unit": "GLUPS",
                    "ms_per_step": round(e2e_ms / K, 4), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                   "last_residual": last, "overlap": "H2D of step i+1 overlaps compute of step i (side stream)"}
+                   "result": "kernel status + global max|u'-u| of the last iteration (32-byte result block)",
+                   "last_residual": last, "overlap": "H2D of step i+1 overlaps compute of step i (side stream)",
+                   "launches_per_step": (s.total_stats.launches - l0) / max(K, 1)}
+
+            # ---- the same, with the solution field gathered to rank 0 and copied to the host every step ----
+            Kg = max(1, min(K, 4))
+
+            def one_step_gather():
+                r = one_step()
+                f = s.gather(copy=False)                  # fused gather+pack over NVLink, D2H into pinned memory
+                return r, (None if f is None else float(f[0, 0]))
+
+            one_step_gather()
+            torch.cuda.synchronize()
+            ctx.barrier()
+            t0 = time.perf_counter()
+            for _ in range(Kg):
+                one_step_gather()
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            eg_ms = ctx.all_reduce_max((t1 - t0) * 1e3)
+            e2e_gather = {"value": round(cells * gps * Kg / (eg_ms * 1e-3) / 1e9, 3), "unit": "GLUPS", "steps": Kg,
+                          "ms_per_step": round(eg_ms / Kg, 4), "h2d_bytes_per_step": int(h2d),
+                          "d2h_bytes_per_step": int(d2h + (cells * host.element_size() if ctx.rank == 0 else 0)),
+                          "gather": s.last_gather_stats}
 
         if ctx.rank == 0:
             esize = 8 if args.dtype == "fp64" else (0.125 if args.dtype == "bits" else 4)
             cells_gpu = cells // ctx.world
             halo = 0 if ctx.world == 1 else int(2 * (cells // cfg.shape[0]) * esize)
-            roof = metrics.roofline(cells_gpu, gps * K, ms_total, 2 * esize, halo)
+            roof = metrics.roofline(cells_gpu, gps * K, ms_total, 2 * esize, halo, time_block=s.time_block)
             out = {
                 "metric": METRIC, "value": round(value, 3), "unit": "GLUPS", "n_gpus": ctx.world, "steps": K,
                 "warmup": W, "ms_per_step": round(ms_total / K, 4), "higher_is_better": True,
@@ -196,6 +227,7 @@ def main(argv=None) -> int:
             }
             if e2e is not None:
                 out["e2e"] = e2e
+                out["e2e_with_gather"] = e2e_gather
             print(json.dumps(out), flush=True)
     ctx.close()
     return 0

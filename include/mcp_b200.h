@@ -35,7 +35,21 @@ extern "C" {
 
 /* residual modes of the fused kernel */
 #define MCP_RES_NONE 0
-#define MCP_RES_LAST 1 /* residual of the last generation of every time block */
+#define MCP_RES_LAST 1  /* residual of the last generation of every time block (a device-side grid barrier per block) */
+#define MCP_RES_FINAL 2 /* residual of the very last generation of the run only: every other time block runs the
+                         * residual-free row loop on the barrier-free path; still ONE launch */
+
+/* mcp_fused2d_set_option */
+#define MCP_OPT_TIMEOUT_MS 1  /* bound of every in-kernel flag / barrier / TMA wait (default 20000) */
+#define MCP_OPT_DEBUG_FLAGS 2 /* bit 2 (4): per-tile timing trace; bit 3 (8): pseudo-random delays in front of halo
+                               * pushes and publishes (protocol stress tests) */
+#define MCP_OPT_SYNC_MODE 3   /* 0 = choose, 1 = device-side grid barrier between sweeps, 2 = per-chunk dataflow flags */
+
+/* mcp_fused2d_stop_reason: why the last run-to-tolerance ended */
+#define MCP_STOP_NONE 0
+#define MCP_STOP_CONVERGED 1       /* the residual met the tolerance (the run ends one time block later) */
+#define MCP_STOP_MAX_GENERATIONS 2 /* max_generations reached first */
+#define MCP_STOP_SLOT_LIMIT 3      /* the residual history table (16384 time blocks per call) is full: call again */
 
 /* ---- runtime (reference: bring-up/teardown in main(), M:114-144,223-234) ---------------------- */
 const char* mcp_last_error(void);
@@ -150,13 +164,29 @@ int mcp_fused2d_run(mcp_fused2d_plan* plan, int generations, int time_block, int
  * generation count only (M:153,157,186). */
 int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* plan, int max_generations, int time_block, int norm, double tol,
                                  int* generations_done, void* stream);
-/* Queue position q -> (chunk, strip) of the sweep's tile order; returns the position computed back from them. */
+/* Why the last mcp_fused2d_run_to_tolerance ended: MCP_STOP_*.  A caller that sees MCP_STOP_SLOT_LIMIT has not
+ * converged yet and may simply call again. */
+int mcp_fused2d_stop_reason(const mcp_fused2d_plan* plan);
+/* Plan options (MCP_OPT_*); take effect from the next run. */
+int mcp_fused2d_set_option(mcp_fused2d_plan* plan, int option, long long value);
+/* Several ranks on ONE GPU in one cooperative launch (tests, single-GPU boxes): plans[r] is rank r's plan, created
+ * with its neighbours' buffers and flag words as "peer" pointers exactly as across GPUs.  CTA b works for rank
+ * b % n, so the ranks run concurrently and wait on each other's flags like kernels on different GPUs do -- which
+ * separate launches sharing one GPU must never do.  One launch; generations must be a multiple of the time block.
+ * Built for fp32 MDF with time block 4 or 8.  Plans used here must always be advanced through this call.
+ * No counterpart in the reference (it cannot run two ranks on one GPU: no cudaSetDevice, M:114-121). */
+int mcp_fused2d_run_group(mcp_fused2d_plan** plans, int n, int generations, int time_block, int residual_mode,
+                          void* stream);
+/* Queue position q -> (group, strip) of the sweep's tile order; returns the position computed back from them. */
 int mcp_fused2d_tile_at(int n_strips, int n_chunks, int q, int* chunk, int* strip);
 /* Device-free planning (pure host arithmetic, works without a GPU): chunk heights in queue order and strip count
  * that a plan would use for a slab of rows_own x w cells on `grid` CTAs.  Returns the chunk count. */
 int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
                               int chunk_rows, int* rows_out, int max_entries, int* n_strips);
-/* Tile trace (set MCP_DEBUG_FLAGS=4 before creating the plan): duration in ns of every tile of the last sweep, in
+/* Same with the schedule kind: mode 0 = grid-barrier schedule, 1 = barrier-free (dataflow) schedule. */
+int mcp_fused2d_plan_schedule2(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
+                               int chunk_rows, int mode, int* rows_out, int max_entries, int* n_strips);
+/* Tile trace (mcp_fused2d_set_option(plan, MCP_OPT_DEBUG_FLAGS, 4) before the run): duration in ns of every tile of the last sweep, in
  * queue order, with its chunk and strip index.  Returns the number of entries. */
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* plan, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
                            int max_entries);
@@ -170,6 +200,11 @@ int mcp_fused2d_set_parity(mcp_fused2d_plan* plan, int parity);
 int mcp_fused2d_residuals(mcp_fused2d_plan* plan, double* sumsq_max_pairs, int max_entries);
 /* 0 = healthy; otherwise the MCP_ERR_* code a kernel recorded (e.g. halo-flag wait timeout). */
 int mcp_fused2d_status(mcp_fused2d_plan* plan);
+int mcp_fused2d_clear_status(mcp_fused2d_plan* plan);
+/* Enqueue ONE 32-byte copy of the plan's result block into (pinned) host memory behind the runs already on
+ * `stream`: { int32 status; int32 stop_word; int32 sweeps_done; int32 pad; double last_sumsq; double last_max } --
+ * the kernel status and the global residual of the last residual sweep without a blocking call. */
+int mcp_fused2d_result_async(mcp_fused2d_plan* plan, void* host32, void* stream);
 /* Number of kernel launches issued by the plan so far. */
 int64_t mcp_fused2d_launches(const mcp_fused2d_plan* plan);
 int mcp_fused2d_geometry(const mcp_fused2d_plan* plan, int time_block, int* n_strips, int* n_chunks, int* grid,
@@ -241,7 +276,8 @@ int mcp_residual2d_noalloc(int dtype, const void* a_dev, const void* b_dev, int6
 /* ---- gather + pack (reference: print_array, K:115-129; no gather exists in the reference) -------- */
 /* Cast/pack owned rows [row_lo,row_hi) x [0,w) of a pitched buffer into a dense destination (which may be a
  * peer pointer on rank 0): mode 0 = raw copy, 1 = fp64 -> fp32, 2 = int32 cells -> print_array bytes
- * ('0' if cell == 1 else ' ', '\n' after each row; dst row stride w+1). */
+ * ('0' if cell == 1 else ' ', '\n' after each row; dst row stride w+1), 3 = bit-packed life words (dtype
+ * MCP_DTYPE_B1, pitch in words) -> one int32 per cell.  16-byte loads and stores when w % 4 == 0. */
 int mcp_pack_rows(int dtype, int mode, const void* src_dev, int64_t pitch, int w, int row_lo, int row_hi,
                   void* dst_dev, int64_t dst_row0, void* stream);
 
@@ -250,6 +286,13 @@ int mcp_pack_rows(int dtype, int mode, const void* src_dev, int64_t pitch, int w
  * mode 0 = raw copy, 1 = fp64 -> fp32.  A 2-D slab is the case nz = 1. */
 int mcp_pack_block(int dtype, int mode, const void* src_dev, int64_t pitch, int64_t plane_pitch, int z_lo, int nz,
                    int y_lo, int ny, int w, void* dst_dev, int64_t dst_h, int64_t dst_z0, int64_t dst_y0, void* stream);
+
+/* Position-dependent 64-bit checksum of rows [row_lo,row_hi) x [0,w) (global rows grow0 ...): the wrapping sum over
+ * cells of mix64(bits ^ golden * global index), written to the device word out_dev.  Order independent, so the
+ * per-rank checksums of a decomposed field add up (mod 2^64) to the checksum of the whole field: fields of benchmark
+ * size can be compared bit for bit across rank counts and backends without a gather.  No counterpart in the reference. */
+int mcp_checksum2d(int dtype, const void* u_dev, int64_t pitch, int w, int row_lo, int row_hi, int64_t grow0,
+                   void* out_dev, void* stream);
 
 /* ---- CPU reference (host code; works without a GPU) ------------------------------------------------ */
 /* glibc rand() stream exactly as the reference consumes it (K:141-142): fills an h x w int32 grid. */

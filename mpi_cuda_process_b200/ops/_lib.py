@@ -91,6 +91,12 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_create.argtypes = [C.POINTER(FusedDesc), c_void_pp]
     lib.mcp_fused2d_run.argtypes = [vp, i, i, i, vp]
     lib.mcp_fused2d_run_to_tolerance.argtypes = [vp, i, i, i, dbl, C.POINTER(i), vp]
+    lib.mcp_fused2d_stop_reason.argtypes = [vp]
+    lib.mcp_fused2d_set_option.argtypes = [vp, i, C.c_longlong]
+    lib.mcp_fused2d_run_group.argtypes = [c_void_pp, i, i, i, i, vp]
+    lib.mcp_fused2d_plan_schedule2.argtypes = [i, i, i, i, i, i, i, i, i, vp, i, C.POINTER(i)]
+    lib.mcp_fused2d_result_async.argtypes = [vp, vp, vp]
+    lib.mcp_fused2d_clear_status.argtypes = [vp]
     lib.mcp_fused2d_tile_at.argtypes = [i, i, i, C.POINTER(i), C.POINTER(i)]
     lib.mcp_fused2d_plan_schedule.argtypes = [i, i, i, i, i, i, i, i, vp, i, C.POINTER(i)]
     lib.mcp_fused2d_tile_trace.argtypes = [vp, i, vp, vp, vp, i]
@@ -117,6 +123,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_residual2d.argtypes = [i, vp, vp, i64, i, i, i, vp, vp, vp]
     lib.mcp_residual2d_noalloc_max_rows.restype = i
     lib.mcp_residual2d_noalloc.argtypes = [i, vp, vp, i64, i, i, i, vp, vp]
+    lib.mcp_checksum2d.argtypes = [i, vp, i64, i, i, i, i64, vp, vp]
     lib.mcp_pack_rows.argtypes = [i, i, vp, i64, i, i, i, vp, i64, vp]
     lib.mcp_pack_block.argtypes = [i, i, vp, i64, i64, i, i, i, i, i, vp, i64, i64, i64, vp]
 
@@ -125,9 +132,7 @@ def host_lib() -> C.CDLL:
     """CPU reference subset; built on demand with g++ (no CUDA needed)."""
     global _host_lib
     if _host_lib is None:
-        path = _build.host_lib_path()
-        if not path.exists():
-            _build.build_host()
+        path = _build.build_host()          # returns at once when the source hash matches the built library
         _host_lib = C.CDLL(str(path))
         _declare_host(_host_lib)
     return _host_lib
@@ -137,12 +142,14 @@ def cuda_lib() -> C.CDLL:
     """The sm_100a library.  Raises NativeError if it is missing and cannot be built."""
     global _cuda_lib
     if _cuda_lib is None:
-        path = _build.lib_path()
-        if not path.exists():
-            try:
-                _build.build_cuda()
-            except Exception as e:  # pragma: no cover - depends on toolchain
-                raise NativeError(f"libmcp_b200.so is missing and could not be built: {e}") from e
+        # always go through the build: a library left over from older sources (e.g. a changed descriptor layout)
+        # must never be loaded; the call returns at once when the source hash matches
+        import os
+        override = os.environ.get("MCP_B200_LIB")      # development only: load an experimental build of the library
+        try:
+            path = override or _build.build_cuda()
+        except Exception as e:  # pragma: no cover - depends on toolchain
+            raise NativeError(f"libmcp_b200.so is stale or missing and could not be built: {e}") from e
         try:
             _cuda_lib = C.CDLL(str(path))
         except OSError as e:

@@ -34,6 +34,7 @@ CUDA_SOURCES = [
     "residual.cu",
     "residual_noalloc.cu",
     "gather_pack.cu",
+    "checksum.cu",
     "host_ref.cpp",
 ]
 HOST_SOURCES = ["host_ref.cpp"]

@@ -34,7 +34,7 @@
 #include "../../../include/mcp_b200.h"
 #include "common.cuh"
 #include "ptx.cuh"
-#include "stencil_ops.cuh"
+#include "stencil2d_ops.cuh"
 
 namespace mcp {
 
@@ -48,11 +48,17 @@ constexpr int smem_bytes_for(int warps) { return warps * kStages * kStageBytes +
 constexpr int kSmemBytes = smem_bytes_for(kWarpsPerCta);
 // TB = 8 keeps 96 registers of row windows per thread: run 12 warps x 168 registers instead of 16 x 128.
 constexpr int kWarpsTb8 = 8;
+#ifndef MCP_WARPS_F32_TB8
+#define MCP_WARPS_F32_TB8 8
+#endif
+constexpr int kWarpsF32Tb8 = MCP_WARPS_F32_TB8;  // fp32 MDF at TB = 8 (experiment knob)
 __host__ __device__ constexpr int warps_for_tb(int tb) { return tb >= 8 ? kWarpsTb8 : kWarpsPerCta; }
 // Register budget per operator: kind 0 = scalar float cells (12 window registers per level), 1 = Life int32 (cells
 // + horizontal sums, 24 per level), 2 = bit-packed Life (cells + two sum planes, 36 per level).  When the windows of
 // TB levels no longer fit 128 registers the CTA runs 8 warps x up to 255 registers instead of 16 x 128.
 __host__ __device__ constexpr int warps_for(int kind, int tb) {
+    if (kind == 0 && tb >= 8) return kWarpsF32Tb8;
+    if (kind == 3) return warps_for_tb(tb);  // fp64 MDF
     if (kind == 2 && tb == 2) return 12;  // 148 registers: 12 warps x 32 x 148 fits the register file
     return (kind == 2 && tb >= 2) || (kind == 1 && tb >= 4) ? kWarpsTb8 : warps_for_tb(tb);
 }
@@ -60,6 +66,15 @@ constexpr int kMaxResSlots = 16384;
 constexpr int kMaxRanks = MCP_MAX_RANKS;
 constexpr int kResRing = MCP_RES_RING;
 constexpr int kMaxStripFlags = MCP_MAX_STRIPS;
+
+// One 32-byte block per plan that a host reads back with ONE copy after a run.
+struct ResultBlock {
+    int status;       // 0 or the MCP_ERR_* code a kernel recorded
+    int stop_word;    // run-to-tolerance: 0 = keep going, else the number of sweeps this launch executes
+    int sweeps_done;  // sweeps actually executed by the last launch
+    int pad;
+    double last_sumsq, last_max;  // global residual of the last residual sweep
+};
 
 struct Fused2dParams {
     void* buf[2];
@@ -82,7 +97,8 @@ struct Fused2dParams {
     int* status;
     double* partials;  // [2][n_tiles][2]
     double* res_out;   // [kMaxResSlots][2]
-    const int* chunk_y;  // [n_chunks + 1] local row boundaries of the row chunks (host-built schedule)
+    ResultBlock* result;  // status / stop word / executed sweeps / last global residual, read back in one copy
+    unsigned* res_count;  // tiles of the residual sweep that have delivered their partial (barrier-free path)
     // cross-rank residual all-reduce over NVLink: every rank stores its (sumsq, max) into slot [seq % ring][rank] of
     // every rank's inbox, bumps that rank's arrival counter, then sums its own inbox in rank order
     double* peer_inbox[kMaxRanks];
@@ -94,7 +110,6 @@ struct Fused2dParams {
     const unsigned long long* res_flag;
     unsigned long long res_seq_base;
     int* stop_word;    // 0 = keep going, else total number of sweeps this launch executes
-    int* sweeps_done;  // sweeps actually executed by this launch
     double stop_thresh;
     int stop_mode;  // 0 none, 1: stop when max|d| <= thresh, 2: stop when sum d^2 <= thresh
     int world, rank;
@@ -107,248 +122,29 @@ struct Fused2dParams {
     int own_lo, own_hi;
     int ylo, yhi, xlo, xhi;
     int G, up_ghost_row;
-    int n_strips, n_chunks;
+    int n_strips, n_chunks, chunk_r;  // a tile = one column strip x one row chunk of chunk_r rows (chunk_row)
     int sweeps, first_parity, res_slot0;
+    int res_first_sweep;  // sweeps >= this accumulate the residual (0 = every sweep, sweeps - 1 = the last one only)
     int debug_flags;
     int sync_mode;  // 1 = grid barrier between sweeps, 2 = per-tile dataflow flags (no barrier)
 };
 
-// ------------------------------------------------------------------------------------------ operators
+// operators: stencil2d_ops.cuh
 
-// Column masks of the scalar-cell operators: one bit per vector component.
-template <int VEC_>
-struct ComponentMask {
-    using Mask = unsigned;
-    static constexpr int CPE = 1;  // cells per storage element
-    static __device__ __forceinline__ Mask full_mask() { return 0xfu; }
-    static __device__ __forceinline__ bool any(Mask m) { return m != 0u; }
-    // component v of the lane's vector is cell cx + v
-    static __device__ __forceinline__ Mask col_mask(int cx, int xlo, int xhi) {
-        Mask m = 0;
-#pragma unroll
-        for (int v = 0; v < VEC_; ++v) {
-            const int gx = cx + v;
-            if (gx < xlo || gx > xhi) m |= 1u << v;
-        }
-        return m;
-    }
-};
 
-struct MdfF32 : ComponentMask<4> {
-    using T = float;
-    using V = float4;
-    static constexpr int VEC = 4;
-    struct Row {
-        V v;
-    };
-    static __device__ __forceinline__ Row make_row(const V& raw) { return Row{raw}; }
-    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
-        const float wl = __shfl_up_sync(0xffffffffu, c.v.w, 1);
-        const float er = __shfl_down_sync(0xffffffffu, c.v.x, 1);
-        V o;
-        o.x = mdf_cell(c.v.x, n.v.x, s.v.x, wl, c.v.y);
-        o.y = mdf_cell(c.v.y, n.v.y, s.v.y, c.v.x, c.v.z);
-        o.z = mdf_cell(c.v.z, n.v.z, s.v.z, c.v.y, c.v.w);
-        o.w = mdf_cell(c.v.w, n.v.w, s.v.w, c.v.z, er);
-        return o;
-    }
-    static __device__ __forceinline__ V select(unsigned m, const V& keep, const V& upd) {
-        V o;
-        o.x = (m & 1u) ? keep.x : upd.x;
-        o.y = (m & 2u) ? keep.y : upd.y;
-        o.z = (m & 4u) ? keep.z : upd.z;
-        o.w = (m & 8u) ? keep.w : upd.w;
-        return o;
-    }
-    // residual contribution of 4 cells: differences and their squares in fp32 (the field's own precision),
-    // one conversion per vector, accumulation across rows in fp64
-    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
-        const float d0 = __fsub_rn(a.x, b.x), d1 = __fsub_rn(a.y, b.y);
-        const float d2 = __fsub_rn(a.z, b.z), d3 = __fsub_rn(a.w, b.w);
-        float q = __fmul_rn(d0, d0);
-        q = __fmaf_rn(d1, d1, q);
-        q = __fmaf_rn(d2, d2, q);
-        q = __fmaf_rn(d3, d3, q);
-        ss += (double)q;
-        const float m = fmaxf(fmaxf(fabsf(d0), fabsf(d1)), fmaxf(fabsf(d2), fabsf(d3)));
-        mx = fmax(mx, (double)m);
-    }
-};
-
-struct MdfF64 : ComponentMask<2> {
-    using T = double;
-    using V = double2;
-    static constexpr int VEC = 2;
-    struct Row {
-        V v;
-    };
-    static __device__ __forceinline__ Row make_row(const V& raw) { return Row{raw}; }
-    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
-        const double wl = __shfl_up_sync(0xffffffffu, c.v.y, 1);
-        const double er = __shfl_down_sync(0xffffffffu, c.v.x, 1);
-        V o;
-        o.x = mdf_cell(c.v.x, n.v.x, s.v.x, wl, c.v.y);
-        o.y = mdf_cell(c.v.y, n.v.y, s.v.y, c.v.x, er);
-        return o;
-    }
-    static __device__ __forceinline__ V select(unsigned m, const V& keep, const V& upd) {
-        V o;
-        o.x = (m & 1u) ? keep.x : upd.x;
-        o.y = (m & 2u) ? keep.y : upd.y;
-        return o;
-    }
-    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
-        const double d0 = a.x - b.x, d1 = a.y - b.y;
-        ss = fma(d0, d0, ss); ss = fma(d1, d1, ss);
-        mx = fmax(mx, fmax(fabs(d0), fabs(d1)));
-    }
-};
-
-struct LifeI32 : ComponentMask<4> {
-    using T = int;
-    using V = int4;
-    static constexpr int VEC = 4;
-    struct Row {
-        V v;   // cells
-        V hs;  // horizontal 3-sums (left + self + right)
-    };
-    static __device__ __forceinline__ Row make_row(const V& raw) {
-        const int wl = __shfl_up_sync(0xffffffffu, raw.w, 1);
-        const int er = __shfl_down_sync(0xffffffffu, raw.x, 1);
-        Row r;
-        r.v = raw;
-        const int xy = raw.x + raw.y, zw = raw.z + raw.w;
-        r.hs.x = wl + xy;
-        r.hs.y = xy + raw.z;
-        r.hs.z = raw.y + zw;
-        r.hs.w = zw + er;
-        return r;
-    }
-    static __device__ __forceinline__ int rule(int n, int c) { return life_rule(n, c); }
-    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
-        V o;
-        o.x = rule(n.hs.x + s.hs.x + c.hs.x - c.v.x, c.v.x);
-        o.y = rule(n.hs.y + s.hs.y + c.hs.y - c.v.y, c.v.y);
-        o.z = rule(n.hs.z + s.hs.z + c.hs.z - c.v.z, c.v.z);
-        o.w = rule(n.hs.w + s.hs.w + c.hs.w - c.v.w, c.v.w);
-        return o;
-    }
-    static __device__ __forceinline__ V select(unsigned m, const V& keep, const V& upd) {
-        V o;
-        o.x = (m & 1u) ? keep.x : upd.x;
-        o.y = (m & 2u) ? keep.y : upd.y;
-        o.z = (m & 4u) ? keep.z : upd.z;
-        o.w = (m & 8u) ? keep.w : upd.w;
-        return o;
-    }
-    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
-        const int d0 = a.x - b.x, d1 = a.y - b.y, d2 = a.z - b.z, d3 = a.w - b.w;
-        const int q = d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
-        ss += (double)q;
-        mx = fmax(mx, q ? 1.0 : 0.0);
-    }
-};
-
-// Bit-packed Game of Life: one cell per bit, 32 cells per 32-bit word (cell x = bit x%32 of word x/32), so a lane's
-// 16-byte vector holds 128 cells and a warp row 4096.  Same rule as LifeI32 (kernel.cu:61,66), evaluated for 32 cells
-// at a time with bit-sliced adders.  The optional fast path of SURVEY section 7.1; the reference stores one int per cell.
-struct LifeB1 {
-    using T = unsigned;
-    using V = uint4;
-    static constexpr int VEC = 4;   // storage elements per lane
-    static constexpr int CPE = 32;  // cells per storage element
-    using Mask = uint4;             // one bit per cell: 1 = keep the old value
-    struct Row {
-        V v;       // cells
-        V s0, s1;  // per cell: (s1:s0) = west + self + east (0..3)
-    };
-    static __device__ __forceinline__ Mask full_mask() {
-        return make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-    }
-    static __device__ __forceinline__ bool any(const Mask& m) { return (m.x | m.y | m.z | m.w) != 0u; }
-    // bits of the word holding cells [c0, c0+32) that lie outside [xlo, xhi]
-    static __device__ __forceinline__ unsigned word_mask(int c0, int xlo, int xhi) {
-        unsigned keep = 0u;  // bits inside [xlo, xhi] -> evolve
-        const int lo = max(xlo, c0), hi = min(xhi, c0 + 31);
-        if (lo <= hi) {
-            const int n = hi - lo + 1;
-            const unsigned run = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
-            keep = run << (lo - c0);
-        }
-        return ~keep;
-    }
-    static __device__ __forceinline__ Mask col_mask(int cx, int xlo, int xhi) {
-        // cx = index of the lane's first storage element; element e holds cells 32e .. 32e+31
-        return make_uint4(word_mask((cx + 0) * 32, xlo, xhi), word_mask((cx + 1) * 32, xlo, xhi),
-                          word_mask((cx + 2) * 32, xlo, xhi), word_mask((cx + 3) * 32, xlo, xhi));
-    }
-    static __device__ __forceinline__ unsigned maj(unsigned a, unsigned b, unsigned c) { return (a & b) | (c & (a ^ b)); }
-    static __device__ __forceinline__ Row make_row(const V& raw) {
-        const unsigned prevw = __shfl_up_sync(0xffffffffu, raw.w, 1);    // word to the west of .x
-        const unsigned nextx = __shfl_down_sync(0xffffffffu, raw.x, 1);  // word to the east of .w
-        Row r;
-        r.v = raw;
-        const unsigned c[4] = {raw.x, raw.y, raw.z, raw.w};
-        const unsigned wprev[4] = {prevw, raw.x, raw.y, raw.z};
-        const unsigned enext[4] = {raw.y, raw.z, raw.w, nextx};
-        unsigned s0[4], s1[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const unsigned W = (c[k] << 1) | (wprev[k] >> 31);  // west neighbour of every cell of the word
-            const unsigned E = (c[k] >> 1) | (enext[k] << 31);  // east neighbour
-            s0[k] = W ^ c[k] ^ E;
-            s1[k] = maj(W, c[k], E);
-        }
-        r.s0 = make_uint4(s0[0], s0[1], s0[2], s0[3]);
-        r.s1 = make_uint4(s1[0], s1[1], s1[2], s1[3]);
-        return r;
-    }
-    static __device__ __forceinline__ unsigned word(unsigned n0, unsigned n1, unsigned c0, unsigned c1, unsigned s0,
-                                                    unsigned s1, unsigned centre) {
-        // total (0..9, centre included) = l + 2*t1 + 4*t2 + 8*t3
-        const unsigned l = n0 ^ c0 ^ s0, cl = maj(n0, c0, s0);
-        const unsigned h = n1 ^ c1 ^ s1, ch = maj(n1, c1, s1);
-        const unsigned t1 = h ^ cl, c2 = h & cl;
-        const unsigned t2 = ch ^ c2, t3 = ch & c2;
-        // alive next iff total == 3, or total == 4 and alive now  (= 3 neighbours, or 2 neighbours and alive)
-        return ~t3 & ((l & t1 & ~t2) | (~l & ~t1 & t2 & centre));
-    }
-    static __device__ __forceinline__ V update(const Row& n, const Row& c, const Row& s) {
-        return make_uint4(word(n.s0.x, n.s1.x, c.s0.x, c.s1.x, s.s0.x, s.s1.x, c.v.x),
-                          word(n.s0.y, n.s1.y, c.s0.y, c.s1.y, s.s0.y, s.s1.y, c.v.y),
-                          word(n.s0.z, n.s1.z, c.s0.z, c.s1.z, s.s0.z, s.s1.z, c.v.z),
-                          word(n.s0.w, n.s1.w, c.s0.w, c.s1.w, s.s0.w, s.s1.w, c.v.w));
-    }
-    static __device__ __forceinline__ V select(const Mask& m, const V& keep, const V& upd) {
-        return make_uint4((keep.x & m.x) | (upd.x & ~m.x), (keep.y & m.y) | (upd.y & ~m.y),
-                          (keep.z & m.z) | (upd.z & ~m.z), (keep.w & m.w) | (upd.w & ~m.w));
-    }
-    static __device__ __forceinline__ void accum(const V& a, const V& b, double& ss, double& mx) {
-        const int q = __popc(a.x ^ b.x) + __popc(a.y ^ b.y) + __popc(a.z ^ b.z) + __popc(a.w ^ b.w);
-        ss += (double)q;  // changed cells: (a-b)^2 is 0 or 1
-        mx = fmax(mx, q ? 1.0 : 0.0);
-    }
-};
-
-template <class V>
-__device__ __forceinline__ V bitcast_v(const uint4& u) {
-    static_assert(sizeof(V) == 16, "vector must be 16 bytes");
-    V v;
-    memcpy(&v, &u, 16);
-    return v;
+// Schedule arithmetic shared by the host plan and the kernel (no tables: a tile start costs no dependent loads).
+// n_chunks - 1 chunks of chunk_r rows and a last one that takes the remainder (chunk_r <= its height < 2 chunk_r).
+__host__ __device__ __forceinline__ int chunk_row_of(int own_lo, int rows, int n_chunks, int chunk_r, int c) {
+    return c < n_chunks ? own_lo + c * chunk_r : own_lo + rows;
 }
-template <class V>
-__device__ __forceinline__ uint4 bitcast_u(const V& v) {
-    uint4 u;
-    memcpy(&u, &v, 16);
-    return u;
-}
-
-__host__ __device__ constexpr int mod3(int x) { return ((x % 3) + 3) % 3; }
 
 // ------------------------------------------------------------------------------------------ waits
 
 __device__ __forceinline__ bool aborted(const Fused2dParams& p) { return *((volatile int*)p.status) != 0; }
+
+__device__ __forceinline__ int chunk_row(const Fused2dParams& p, int c) {
+    return chunk_row_of(p.own_lo, p.own_hi - p.own_lo, p.n_chunks, p.chunk_r, c);
+}
 
 // Lane-0 style bounded acquire spin on a monotonic counter.  Returns false on abort/timeout.
 __device__ __noinline__ bool wait_counter_sys(const Fused2dParams& p, const unsigned long long* ctr,
@@ -369,12 +165,63 @@ __device__ __noinline__ bool wait_counter_sys(const Fused2dParams& p, const unsi
     return true;
 }
 
-__device__ __noinline__ void grid_barrier(const Fused2dParams& p, unsigned long long& epoch) {
+// Bounded acquire spin at GPU scope on a per-(chunk, strip) completion word.
+__device__ __noinline__ bool wait_tile_done(const Fused2dParams& p, const unsigned* word, unsigned need) {
+    auto ld = [&]() {
+        unsigned v;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+        return v;
+    };
+    if (ld() >= need) return true;
+    const unsigned long long t0 = ptx::globaltimer_ns();
+    unsigned spins = 0;
+    while (ld() < need) {
+        if ((++spins & 255u) == 0) {
+            if (aborted(p)) return false;
+            if (ptx::globaltimer_ns() - t0 > p.timeout_ns) {
+                atomicCAS(p.status, 0, MCP_ERR_TIMEOUT);
+                return false;
+            }
+        }
+    }
+    return true;
+}
+
+// TMA completion wait.  The fast path is one try_wait; a wait that keeps failing (a faulted or never-issued copy)
+// gives up with MCP_ERR_TIMEOUT instead of spinning until the watchdog.
+__device__ __forceinline__ void mbar_wait_bounded(const Fused2dParams& p, uint64_t* bar, uint32_t parity) {
+    if (ptx::mbar_try_wait(bar, parity)) return;
+    unsigned spins = 0;
+    unsigned long long t0 = 0;
+    while (!ptx::mbar_try_wait(bar, parity)) {
+        if ((++spins & 0x3fffu) == 0) {
+            const unsigned long long now = ptx::globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            if (now - t0 > p.timeout_ns) {
+                atomicCAS(p.status, 0, MCP_ERR_TIMEOUT);
+                return;
+            }
+        }
+    }
+}
+
+// Test hook (debug_flags & 8): pseudo-random stalls of 5..200 us in front of halo pushes and publishes, so that the
+// flag protocol is exercised with ranks and tiles far out of step.
+__device__ __noinline__ void injected_delay(const Fused2dParams& p, unsigned salt) {
+    unsigned h = (unsigned)p.rank * 0x9e3779b9u ^ salt * 0x85ebca6bu;
+    h ^= h >> 15; h *= 0x2c1b3c6du; h ^= h >> 12; h *= 0x297a2d39u; h ^= h >> 15;
+    if ((h & 7u) != 0u) return;  // one event in eight is delayed
+    const unsigned long long dur = 5000ull + (unsigned long long)((h >> 3) % 195000u);
+    const unsigned long long t0 = ptx::globaltimer_ns();
+    while (ptx::globaltimer_ns() - t0 < dur) __nanosleep(1000);
+}
+
+__device__ __noinline__ void grid_barrier(const Fused2dParams& p, unsigned long long& epoch, int ncta) {
     __syncthreads();
     if (threadIdx.x == 0) {
         ptx::fence_proxy_async();  // our generic-proxy stores are read by other CTAs' TMA loads next sweep
         __threadfence();
-        const unsigned long long target = p.bar_base + (epoch + 1ull) * gridDim.x;
+        const unsigned long long target = p.bar_base + (epoch + 1ull) * (unsigned long long)ncta;
         ptx::red_add_release_gpu(p.grid_bar, 1ull);
         const unsigned long long t0 = ptx::globaltimer_ns();
         unsigned spins = 0;
@@ -434,16 +281,16 @@ __device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const u
             // Pre-roll: level t's first meaningful row appears at input counter 2t; anything earlier would be
             // computed from rows that do not exist and is never read by a meaningful cell -- skip it.
             if (GENERAL && (cbase + j < 2 * t)) continue;
-            V res = Op::update(L[t - 1][sn], L[t - 1][sc], L[t - 1][ss]);
+            typename Op::Out res = Op::update(L[t - 1][sn], L[t - 1][sc], L[t - 1][ss]);
             if (GENERAL) {
                 const int gy = gy_base + j - t;
                 const typename Op::Mask m = (gy < ylo || gy > yhi) ? Op::full_mask() : colfix;
-                res = Op::select(m, L[t - 1][sc].v, res);
+                res = Op::sel(m, L[t - 1][sc], res);
             } else if (MODE == 1) {
-                res = Op::select(colfix, L[t - 1][sc].v, res);
+                res = Op::sel(colfix, L[t - 1][sc], res);
             }
             if (t < TB) {
-                L[t < TB ? t : 0][sc] = Op::make_row(res);
+                L[t < TB ? t : 0][sc] = Op::to_row(res);
             } else {
                 bool row_ok = true;
                 if (GENERAL) {
@@ -451,12 +298,47 @@ __device__ __forceinline__ void stage_rows(typename Op::Row (&L)[TB][3], const u
                     row_ok = (c >= 2 * TB) && (c < n_in);
                 }
                 if (RES) {
-                    if (row_ok && lane_valid) Op::accum(res, L[TB - 1][sc].v, rs, rm);
+                    if (row_ok && lane_valid) Op::acc(res, L[TB - 1][sc], rs, rm);
                 }
-                st_global_v4_pred(optr, bitcast_u<V>(res), lane_store && row_ok);
+                st_global_v4_pred(optr, bitcast_u<V>(Op::to_vec(res)), lane_store && row_ok);
             }
         }
         optr += pitch;  // one output row per input row, whether or not it was stored
+    }
+}
+
+// Tile order within a sweep: row chunks from the outside in (0, nc-1, 1, nc-2, ...), all strips of a chunk
+// together.  The chunks on the slab cuts come first so that their halo rows leave early and the transfer overlaps
+// the rest of the sweep; a chunk's neighbours in the previous sweep were drawn equally early, so on the barrier-free
+// path an early ticket never waits for a late one.
+__host__ __device__ __forceinline__ void decode_tile(int q, int ns, int ng, int& group, int& strip) {
+    const int gi = q / ns;
+    strip = q - gi * ns;
+    group = (gi & 1) ? ng - 1 - (gi >> 1) : (gi >> 1);
+}
+
+// Inverse of decode_tile.
+__host__ __device__ __forceinline__ int encode_tile(int group, int strip, int ns, int ng) {
+    const int gi = (group <= ng - 1 - group) ? 2 * group : 2 * (ng - 1 - group) + 1;
+    return gi * ns + strip;
+}
+
+// Ghost rows this tile reads were written by the neighbour GPU during its previous sweep: wait for its flags.
+__device__ __forceinline__ void wait_ghost(const Fused2dParams& p, const int dir, const int sw, const int strip,
+                                           const int lane) {
+    const unsigned long long need = p.seq_base + (unsigned long long)sw;  // sweeps the neighbour must have done
+    if (need == 0) return;
+    if (p.strip_flags != nullptr) {
+        const unsigned long long* row = p.strip_flags + dir * kMaxStripFlags;
+        if (sw == 0 && p.prev_n_strips != p.n_strips) {  // the previous launch cut its strips differently
+            for (int s2 = lane; s2 < p.prev_n_strips; s2 += 32) wait_counter_sys(p, &row[s2], need);
+        } else if (lane < 3) {
+            const int s2 = strip + lane - 1;
+            if (s2 >= 0 && s2 < p.n_strips) wait_counter_sys(p, &row[s2], need);
+        }
+    } else if (lane == 0) {
+        wait_counter_sys(p, &p.my_flags[dir],
+                         (dir == 0 ? p.flag_base_up : p.flag_base_dn) + (unsigned long long)sw * p.n_strips);
     }
 }
 
@@ -505,7 +387,7 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
 
     for (int i = 0; i < n_it; ++i) {
         const uint32_t st = it % kStages, par = (it / kStages) & 1u;
-        ptx::mbar_wait(&bars[st], par);
+        mbar_wait_bounded(p, &bars[st], par);
         const uint8_t* sp = my_smem + st * kStageBytes + lane * 16;
         const int cbase = i * kRowsPerStage;
         const int gy_base = p.row0 + ys + cbase;  // global row of this stage's first input row
@@ -545,48 +427,102 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
     }
 }
 
-// Tile order within a sweep: chunks from the outside in (0, nc-1, 1, nc-2, ...), all strips of a chunk together.
-// The slab-cut chunks come first so their halo pushes overlap the rest of the sweep, and a chunk's neighbours in
-// the previous sweep were finished equally early, so the barrier-free path never has an early ticket waiting for
-// a late one.
-__host__ __device__ __forceinline__ void decode_tile(int q, int ns, int nc, int& chunk, int& strip) {
-    const int ci = q / ns;
-    strip = q - ci * ns;
-    chunk = (ci & 1) ? nc - 1 - (ci >> 1) : (ci >> 1);
-}
-
-// Inverse of decode_tile.
-__host__ __device__ __forceinline__ int encode_tile(int chunk, int strip, int ns, int nc) {
-    const int ci = (chunk <= nc - 1 - chunk) ? 2 * chunk : 2 * (nc - 1 - chunk) + 1;
-    return ci * ns + strip;
-}
-
-// Bounded acquire spin at GPU scope on a per-tile completion word.
-__device__ __noinline__ bool wait_tile_done(const Fused2dParams& p, const unsigned* word, unsigned need) {
-    auto ld = [&]() {
-        unsigned v;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
-        return v;
-    };
-    if (ld() >= need) return true;
-    const unsigned long long t0 = ptx::globaltimer_ns();
-    unsigned spins = 0;
-    while (ld() < need) {
-        if ((++spins & 255u) == 0) {
-            if (aborted(p)) return false;
-            if (ptx::globaltimer_ns() - t0 > p.timeout_ns) {
-                atomicCAS(p.status, 0, MCP_ERR_TIMEOUT);
-                return false;
+// Fixed-order reduction of the per-tile (sum d^2, max |d|) partials of one sweep by ONE warp, then the cross-rank
+// all-reduce over NVLink (P2P inbox or NVLS multimem), the stop decision and the result block.  The order never
+// depends on which warp runs it or on timing, so every rank and every run obtains the same bits.
+__device__ __noinline__ void reduce_and_exchange(const Fused2dParams& p, const double* partials, const int n_tiles,
+                                                 const int sw, const int lane) {
+    double a = 0.0, b = 0.0;
+    for (int i = lane; i < n_tiles; i += 32) {
+        a += __ldcg(&partials[2 * i]);
+        b = fmax(b, __ldcg(&partials[2 * i + 1]));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+    }
+    if (lane == 0) {
+        double sa = a, sb = b;
+        if (p.world > 1 && p.nvls_mc != nullptr) {
+            // NVLS all-reduce: every rank stores its pair into its OWN copy of the slot, one multimem.red
+            // bumps the arrival counter of every GPU through the switch, and multimem.ld_reduce pulls the
+            // sum / max of all copies through the switch in one load each.
+            const unsigned long long seq = p.res_seq_base + (unsigned long long)(sw - p.res_first_sweep);
+            const size_t off = 128 + (size_t)(seq % kResRing) * 16;
+            *reinterpret_cast<volatile double*>(p.nvls_local + off) = sa;
+            *reinterpret_cast<volatile unsigned long long*>(p.nvls_local + off + 8) =
+                (unsigned long long)__double_as_longlong(sb);  // sb >= 0: bit pattern order == value order
+            ptx::fence_acq_rel_sys();
+            ptx::multimem_red_add_release_u64(reinterpret_cast<unsigned long long*>(p.nvls_mc), 1ull);
+            if (wait_counter_sys(p, reinterpret_cast<const unsigned long long*>(p.nvls_local),
+                                 (seq + 1ull) * (unsigned long long)p.world)) {
+                sa = ptx::multimem_ld_reduce_add_f64(reinterpret_cast<const double*>(p.nvls_mc + off));
+                sb = __longlong_as_double((long long)ptx::multimem_ld_reduce_max_u64(
+                    reinterpret_cast<const unsigned long long*>(p.nvls_mc + off + 8)));
+            }
+        } else if (p.world > 1 && p.peer_inbox[0] != nullptr) {
+            // all-reduce over peer memory: push, signal, wait for everybody, sum in rank order
+            const unsigned long long seq = p.res_seq_base + (unsigned long long)(sw - p.res_first_sweep);
+            const size_t off = ((size_t)(seq % kResRing) * kMaxRanks + (size_t)p.rank) * 2;
+            for (int r = 0; r < p.world; ++r) {
+                p.peer_inbox[r][off] = sa;
+                p.peer_inbox[r][off + 1] = sb;
+            }
+            ptx::fence_acq_rel_sys();
+            for (int r = 0; r < p.world; ++r) ptx::red_add_release_sys(p.peer_res_flag[r], 1ull);
+            if (wait_counter_sys(p, p.res_flag, (seq + 1ull) * (unsigned long long)p.world)) {
+                const volatile double* in = p.peer_inbox[p.rank] + (size_t)(seq % kResRing) * kMaxRanks * 2;
+                sa = 0.0;
+                sb = 0.0;
+                for (int r = 0; r < p.world; ++r) {
+                    sa += in[2 * r];
+                    sb = fmax(sb, in[2 * r + 1]);
+                }
+            }
+        }
+        const int slot = p.res_slot0 + (sw - p.res_first_sweep);
+        if (slot < kMaxResSlots) {
+            p.res_out[2 * slot] = sa;
+            p.res_out[2 * slot + 1] = sb;
+        }
+        p.result->last_sumsq = sa;
+        p.result->last_max = sb;
+        if (p.stop_mode != 0 && *((volatile int*)p.stop_word) == 0) {
+            const bool conv = p.stop_mode == 1 ? (sb <= p.stop_thresh) : (sa <= p.stop_thresh);
+            if (conv) {
+                *((volatile int*)p.stop_word) = sw + 2;  // one more sweep runs while this is published
+                __threadfence();
             }
         }
     }
-    return true;
+    __syncwarp();
 }
 
+// Before the kernel ends: every halo row the neighbours push towards this rank during this launch has landed (their
+// boundary chunks of the LAST sweep raise the flags this waits for).  After that the host may overwrite the slab
+// (next input) or launch again without any host-side barrier between the ranks.
+__device__ __noinline__ void drain_incoming(const Fused2dParams& p, const int lane, const int sweeps_run) {
+    const unsigned long long need = p.seq_base + (unsigned long long)sweeps_run;
+#pragma unroll
+    for (int dir = 0; dir < 2; ++dir) {
+        if ((dir == 0 ? p.up_buf[0] : p.dn_buf[0]) == nullptr) continue;
+        if (p.strip_flags != nullptr) {
+            const unsigned long long* row = p.strip_flags + dir * kMaxStripFlags;
+            for (int s2 = lane; s2 < p.n_strips; s2 += 32) wait_counter_sys(p, &row[s2], need);
+        } else if (lane == 0) {
+            wait_counter_sys(p, &p.my_flags[dir],
+                             (dir == 0 ? p.flag_base_up : p.flag_base_dn) + (unsigned long long)sweeps_run * p.n_strips);
+        }
+    }
+    __syncwarp();
+}
+
+// The kernel body; `cta` / `ncta` are this CTA's index and the CTA count of ITS rank (the whole grid in a normal
+// launch; a slice of it when several ranks are emulated inside one launch, see fused2d_group_kernel).
 template <class Op, int TB, bool RES, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 1)
-fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ Fused2dParams p) {
+__device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUtensorMap* tmB, const Fused2dParams& p,
+                                             const int cta, const int ncta) {
     using T = typename Op::T;
     constexpr int VEC = Op::VEC;
     constexpr int M = (TB + VEC * Op::CPE - 1) / (VEC * Op::CPE);
@@ -596,30 +532,30 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t* my_smem = smem + warp * (kStages * kStageBytes);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WARPS * kStages * kStageBytes) + warp * kStages;
-    __shared__ double red_ss[WARPS], red_mx[WARPS];
 
     if (lane == 0) {
         for (int s = 0; s < kStages; ++s) ptx::mbar_init(&bars[s], 1);
         ptx::mbar_fence_init();
-        ptx::prefetch_tensormap(&tmA);
-        ptx::prefetch_tensormap(&tmB);
+        ptx::prefetch_tensormap(tmA);
+        ptx::prefetch_tensormap(tmB);
     }
     __syncthreads();
 
-    const int NW = gridDim.x * WARPS;
+    const int NW = ncta * WARPS;
     const int n_tiles = p.n_strips * p.n_chunks;
     uint32_t it = 0;
 
-    const bool dataflow = !RES && p.sync_mode == 2;
-    // One tile of one sweep: wait for what it reads, run it, publish what it wrote.
-    auto run_tile = [&](const int sw, const int q, double* partials) {
+    const bool dataflow = p.sync_mode == 2;
+    // One tile of one sweep.  RES_NOW: this sweep accumulates the residual (a compile-time copy of the row loop).
+    auto run_tile = [&](const int sw, const int q, double* partials, auto res_now) {
+        constexpr bool RES_NOW = decltype(res_now)::value;
         const int par = (p.first_parity + sw) & 1;
-        const CUtensorMap* tm_in = par ? &tmB : &tmA;
+        const CUtensorMap* tm_in = par ? tmB : tmA;
         T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
         int chunk, strip;
         decode_tile(q, p.n_strips, p.n_chunks, chunk, strip);
-        const int y0 = __ldg(&p.chunk_y[chunk]);
-        const int y1 = __ldg(&p.chunk_y[chunk + 1]);
+        const int y0 = chunk_row(p, chunk);
+        const int y1 = chunk_row(p, chunk + 1);
         const int x_ld = strip * OUTW - M * VEC;
         const bool top = (chunk == 0), bot = (chunk == p.n_chunks - 1);
         T* up_out = top ? reinterpret_cast<T*>(p.up_buf[par ^ 1]) : nullptr;
@@ -631,32 +567,10 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // One lane per neighbour, so the nine acquire loads are in flight together.
             const int c2 = chunk + lane / 3 - 1, s2 = strip + lane % 3 - 1;
             if (c2 >= 0 && c2 < p.n_chunks && s2 >= 0 && s2 < p.n_strips)
-                wait_tile_done(p, &p.tile_done[encode_tile(c2, s2, p.n_strips, p.n_chunks)], (unsigned)sw);
+                wait_tile_done(p, &p.tile_done[c2 * p.n_strips + s2], (unsigned)sw);
         }
-        // Ghost rows this tile reads were written by the neighbour GPU during its previous sweep.
-        if (p.strip_flags != nullptr) {
-            const unsigned long long need = p.seq_base + (unsigned long long)sw;  // sweeps the neighbour must have done
-            if (need > 0) {
-                const bool regroup = (sw == 0 && p.prev_n_strips != p.n_strips);  // strips were cut differently
-#pragma unroll
-                for (int dir = 0; dir < 2; ++dir) {
-                    if ((dir == 0 ? up_out : dn_out) == nullptr) continue;
-                    const unsigned long long* row = p.strip_flags + dir * kMaxStripFlags;
-                    if (regroup) {
-                        for (int s2 = lane; s2 < p.prev_n_strips; s2 += 32) wait_counter_sys(p, &row[s2], need);
-                    } else if (lane < 3) {
-                        const int s2 = strip + lane - 1;
-                        if (s2 >= 0 && s2 < p.n_strips) wait_counter_sys(p, &row[s2], need);
-                    }
-                }
-            }
-        } else if (lane == 0) {
-            bool ok = true;
-            if (up_out != nullptr)
-                ok = wait_counter_sys(p, &p.my_flags[0], p.flag_base_up + (unsigned long long)sw * p.n_strips);
-            if (ok && dn_out != nullptr)
-                ok = wait_counter_sys(p, &p.my_flags[1], p.flag_base_dn + (unsigned long long)sw * p.n_strips);
-        }
+        if (up_out != nullptr) wait_ghost(p, 0, sw, strip, lane);
+        if (dn_out != nullptr) wait_ghost(p, 1, sw, strip, lane);
         __syncwarp();
         if (lane == 0) ptx::fence_proxy_async();  // generic-proxy stores (other SMs, peers) -> our TMA loads
         __syncwarp();
@@ -665,10 +579,11 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         double rs = 0.0, rm = 0.0;
         const bool trace = (p.debug_flags & 4) != 0;
         const unsigned long long t_begin = trace ? ptx::globaltimer_ns() : 0ull;
-        process_tile<Op, TB, RES>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
+        if ((p.debug_flags & 8) && (top || bot)) injected_delay(p, (unsigned)(sw * 131071 + strip * 2 + 0));
+        process_tile<Op, TB, RES_NOW>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
         if (trace && lane == 0) p.tile_ns[q] = (unsigned)(ptx::globaltimer_ns() - t_begin);
 
-        if (RES) {
+        if (RES_NOW) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 rs += __shfl_xor_sync(0xffffffffu, rs, o);
@@ -681,11 +596,12 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         // Publish: all lanes' stores (local rows, peer ghost rows) -> one release per consumer.
         __syncwarp();
+        if ((p.debug_flags & 8) && (top || bot)) injected_delay(p, (unsigned)(sw * 131071 + strip * 2 + 1));
         if (lane == 0) {
             if (dataflow) {
                 ptx::fence_proxy_async();
-                __threadfence();
-                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&p.tile_done[q]), "r"((unsigned)(sw + 1))
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&p.tile_done[chunk * p.n_strips + strip]),
+                             "r"((unsigned)(sw + 1))
                              : "memory");
             }
             const unsigned long long done_seq = p.seq_base + (unsigned long long)sw + 1ull;
@@ -718,20 +634,44 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (!aborted(p)) {
                 const int sw = (int)(t / (unsigned long long)n_tiles);
                 const int q = (int)(t - (unsigned long long)sw * n_tiles);
-                run_tile(sw, q, nullptr);
+                bool res_now = false;
+                if constexpr (RES) res_now = sw >= p.res_first_sweep;
+                if constexpr (RES) if (res_now) {
+                    // only the LAST sweep may carry the residual on this path (host-enforced): the last tile to
+                    // finish it reduces the partials and runs the cross-rank exchange
+                    run_tile(sw, q, p.partials, std::true_type{});
+                    unsigned last = 0;
+                    __syncwarp();
+                    if (lane == 0) {
+                        __threadfence();
+                        last = (atomicAdd(p.res_count, 1u) + 1u == (unsigned)n_tiles) ? 1u : 0u;
+                    }
+                    last = __shfl_sync(0xffffffffu, last, 0);
+                    if (last) {
+                        __threadfence();
+                        reduce_and_exchange(p, p.partials, n_tiles, sw, lane);
+                        if (lane == 0) {
+                            *p.res_count = 0u;
+                            p.result->sweeps_done = p.sweeps;
+                        }
+                    }
+                }
+                if (!res_now) run_tile(sw, q, nullptr, std::false_type{});
             }
             t = t_next;
         }
+        if (cta == 0 && warp == 0 && !aborted(p)) drain_incoming(p, lane, p.sweeps);
         return;
     }
 
-    // ---- barrier path: sweeps separated by a device-side grid barrier (always used with the fused residual, so
-    // that CTA 0 can reduce the per-tile partials of a finished sweep)
+    // ---- barrier path: sweeps separated by a device-side grid barrier (used when every sweep carries the residual:
+    // history and run-to-tolerance, where the stop decision of sweep k must reach every CTA before sweep k+2)
     unsigned long long epoch = 0;
     int executed = 0;
     for (int sw = 0; sw < p.sweeps; ++sw) {
+        const bool res_now = RES && sw >= p.res_first_sweep;
         if (RES && p.stop_mode != 0 && sw > 0) {
-            // decided by CTA 0 from the global residual of sweep sw-2 and published before barrier sw-1
+            // decided from the global residual of sweep sw-2 and published before barrier sw-1
             const int s = *((volatile int*)p.stop_word);
             if (s != 0 && sw >= s) break;
         }
@@ -749,91 +689,56 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         int q = grab();
         while (q < n_tiles) {
             const int q_next = grab();
-            if (!aborted(p)) run_tile(sw, q, partials);
+            if (!aborted(p)) {
+                if constexpr (RES) {
+                    if (res_now)
+                        run_tile(sw, q, partials, std::true_type{});
+                    else
+                        run_tile(sw, q, partials, std::false_type{});
+                } else {
+                    run_tile(sw, q, partials, std::false_type{});
+                }
+            }
             q = q_next;
         }
 
-        if (RES || sw + 1 < p.sweeps) grid_barrier(p, epoch);
+        if (res_now || sw + 1 < p.sweeps) grid_barrier(p, epoch, ncta);
         if (aborted(p)) break;
 
-        if (RES && blockIdx.x == 0) {
-            // fixed-order reduction of the per-tile partials -> one (sumsq, max) per sweep
-            double a = 0.0, b = 0.0;
-            for (int i = threadIdx.x; i < n_tiles; i += WARPS * 32) {
-                a += __ldcg(&partials[2 * i]);
-                b = fmax(b, __ldcg(&partials[2 * i + 1]));
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                a += __shfl_xor_sync(0xffffffffu, a, o);
-                b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
-            }
-            if (lane == 0) {
-                red_ss[warp] = a;
-                red_mx[warp] = b;
-            }
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                double sa = 0.0, sb = 0.0;
-                for (int k = 0; k < WARPS; ++k) {
-                    sa += red_ss[k];
-                    sb = fmax(sb, red_mx[k]);
-                }
-                if (p.world > 1 && p.nvls_mc != nullptr) {
-                    // NVLS all-reduce: every rank stores its pair into its OWN copy of the slot, one multimem.red
-                    // bumps the arrival counter of every GPU through the switch, and multimem.ld_reduce pulls the
-                    // sum / max of all copies through the switch in one load each.
-                    const unsigned long long seq = p.res_seq_base + (unsigned long long)sw;
-                    const size_t off = 128 + (size_t)(seq % kResRing) * 16;
-                    *reinterpret_cast<volatile double*>(p.nvls_local + off) = sa;
-                    *reinterpret_cast<volatile unsigned long long*>(p.nvls_local + off + 8) =
-                        (unsigned long long)__double_as_longlong(sb);  // sb >= 0: bit pattern order == value order
-                    ptx::fence_acq_rel_sys();
-                    ptx::multimem_red_add_release_u64(reinterpret_cast<unsigned long long*>(p.nvls_mc), 1ull);
-                    if (wait_counter_sys(p, reinterpret_cast<const unsigned long long*>(p.nvls_local),
-                                         (seq + 1ull) * (unsigned long long)p.world)) {
-                        sa = ptx::multimem_ld_reduce_add_f64(reinterpret_cast<const double*>(p.nvls_mc + off));
-                        sb = __longlong_as_double((long long)ptx::multimem_ld_reduce_max_u64(
-                            reinterpret_cast<const unsigned long long*>(p.nvls_mc + off + 8)));
-                    }
-                } else if (p.world > 1 && p.peer_inbox[0] != nullptr) {
-                    // all-reduce over peer memory: push, signal, wait for everybody, sum in rank order
-                    const unsigned long long seq = p.res_seq_base + (unsigned long long)sw;
-                    const size_t off = ((size_t)(seq % kResRing) * kMaxRanks + (size_t)p.rank) * 2;
-                    for (int r = 0; r < p.world; ++r) {
-                        p.peer_inbox[r][off] = sa;
-                        p.peer_inbox[r][off + 1] = sb;
-                    }
-                    ptx::fence_acq_rel_sys();
-                    for (int r = 0; r < p.world; ++r) ptx::red_add_release_sys(p.peer_res_flag[r], 1ull);
-                    if (wait_counter_sys(p, p.res_flag, (seq + 1ull) * (unsigned long long)p.world)) {
-                        const volatile double* in = p.peer_inbox[p.rank] + (size_t)(seq % kResRing) * kMaxRanks * 2;
-                        sa = 0.0;
-                        sb = 0.0;
-                        for (int r = 0; r < p.world; ++r) {
-                            sa += in[2 * r];
-                            sb = fmax(sb, in[2 * r + 1]);
-                        }
-                    }
-                }
-                const int slot = p.res_slot0 + sw;
-                if (slot < kMaxResSlots) {
-                    p.res_out[2 * slot] = sa;
-                    p.res_out[2 * slot + 1] = sb;
-                }
-                if (p.stop_mode != 0 && *((volatile int*)p.stop_word) == 0) {
-                    const bool conv = p.stop_mode == 1 ? (sb <= p.stop_thresh) : (sa <= p.stop_thresh);
-                    if (conv) {
-                        *((volatile int*)p.stop_word) = sw + 2;  // one more sweep runs while this is published
-                        __threadfence();
-                    }
-                }
-            }
+        if (RES && res_now && cta == 0) {
+            if (warp == 0) reduce_and_exchange(p, partials, n_tiles, sw, lane);
             __syncthreads();
         }
         executed = sw + 1;
     }
-    if (RES && blockIdx.x == 0 && threadIdx.x == 0) *p.sweeps_done = executed;
+    if (cta == 0 && warp == 0) {
+        if (lane == 0) p.result->sweeps_done = executed;
+        if (!aborted(p)) drain_incoming(p, lane, executed);
+    }
+}
+
+template <class Op, int TB, bool RES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ Fused2dParams p) {
+    fused2d_body<Op, TB, RES, WARPS>(&tmA, &tmB, p, (int)blockIdx.x, (int)gridDim.x);
+}
+
+// Several ranks inside ONE cooperative launch on ONE GPU: CTA b works for rank b % n_ranks with the parameters and
+// tensor maps of that rank read from global memory.  The ranks' kernels wait on each other's flags exactly as they do
+// across GPUs (only the pointer values differ), which separate launches sharing one GPU must never do.  Used by the
+// tests to exercise the whole cross-rank protocol (strip flags, residual exchange, drain, timeouts, injected delays)
+// on a single-GPU box.
+struct GroupRankArgs {
+    alignas(64) CUtensorMap tm[2];
+    Fused2dParams p;
+};
+
+template <class Op, int TB, bool RES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) fused2d_group_kernel(const GroupRankArgs* args, const int n_ranks) {
+    const int r = (int)blockIdx.x % n_ranks;
+    fused2d_body<Op, TB, RES, WARPS>(&args[r].tm[0], &args[r].tm[1], args[r].p, (int)blockIdx.x / n_ranks,
+                                     (int)gridDim.x / n_ranks);
 }
 
 // ------------------------------------------------------------------------------------------ host plan
@@ -842,6 +747,19 @@ fused2d_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
 using namespace mcp;
 
+namespace {
+
+constexpr int kMaxChunks = 4096;
+
+// Tile schedule of one (time block, sweep-synchronisation mode) pair.
+struct Geometry {
+    std::vector<int> chunk_y;  // n_chunks + 1 local row boundaries
+    int n_strips = 0, chunk_r = 1;
+    int n_chunks() const { return (int)chunk_y.size() - 1; }
+};
+
+}  // namespace
+
 struct mcp_fused2d_plan {
     mcp_fused2d_desc d;
     int rows_alloc;
@@ -849,21 +767,21 @@ struct mcp_fused2d_plan {
     int grid;
     int parity;
     CUtensorMap tm[2];
-    unsigned long long* grid_bar;
-    int* status;
+    unsigned long long* grid_bar;   // device: [0] grid barrier, [16] tile ticket counter, [32] residual tile counter
+    ResultBlock* result;            // device
     double* partials;
     size_t partials_cap_tiles;
     double* res_out;
-    int* chunk_tab;                 // device: kNumTb tables of kMaxChunks + 1 row boundaries
-    int* stop_words;                // device: [0] stop word, [1] sweeps done
     unsigned* tile_done;            // device: [partials_cap_tiles]
     unsigned* tile_ns;              // device: [partials_cap_tiles] per-tile trace
+    GroupRankArgs* group_args;      // device: parameters of the ranks of an emulated multi-rank launch
     int last_tiles;                 // tile count of the last launch
     unsigned long long res_seq;     // sweeps whose residual has been exchanged so far
     unsigned long long sweep_seq;   // sweeps completed so far (identical on every rank)
     int last_ns;                    // strip count of the previous launch
     int last_generations;           // generations executed by the last run call
-    std::vector<int> chunk_host[4];  // per time block 1,2,4,8
+    int last_stop_reason;           // run-to-tolerance: MCP_STOP_*
+    Geometry geo[4][2];             // [time block 1,2,4,8][0 = grid barrier, 1 = dataflow]
     unsigned long long flag_base_up, flag_base_dn, bar_base, ctr_base;
     int res_slots_used;
     int64_t launches;
@@ -876,7 +794,11 @@ namespace {
 
 int vec_of(int dtype) { return dtype == MCP_DTYPE_F64 ? 2 : 4; }
 
-int op_kind(const mcp_fused2d_desc& d) { return d.dtype == MCP_DTYPE_B1 ? 2 : (d.op == MCP_OP_LIFE ? 1 : 0); }
+int op_kind(const mcp_fused2d_desc& d) {
+    if (d.dtype == MCP_DTYPE_B1) return 2;
+    if (d.op == MCP_OP_LIFE) return 1;
+    return d.dtype == MCP_DTYPE_F64 ? 3 : 0;
+}
 
 int cpe_of(int dtype) { return dtype == MCP_DTYPE_B1 ? 32 : 1; }  // cells per storage element
 
@@ -887,137 +809,237 @@ int outw_rt(int dtype, int tb) {
 }
 
 int max_tb(int op, int dtype) {
+    (void)dtype;
     if (op == MCP_OP_LIFE) return 4;
     return 8;
 }
 
-constexpr int kMaxChunks = 4096;
-
 int tb_index(int tb) { return tb == 1 ? 0 : tb == 2 ? 1 : tb == 4 ? 2 : 3; }
 
-// Row-chunk schedule for the dynamic tile queue.  Tiles are drawn in chunk order, so chunk heights follow a
-// guided self-scheduling curve: tall chunks first (the 2*TB redundant pre-roll rows per chunk stay cheap),
-// short chunks last (the tail of a sweep is one *short* tile).  Used for experiments through MCP_GSS_*; the
-// default schedule (build_chunks) is uniform because the measured gain of the taper was within noise.
-void gss_chunks(int rows, int own_lo, int ns, double NW, int tb, int G, double k, int rmin_mult, int rmax_mult,
-                std::vector<int>* out) {
-    std::vector<int>& y = *out;
-    y.clear();
-    y.push_back(own_lo);
-    const int rmin = std::max(G, rmin_mult * tb);
-    const int rmax = std::max(rmin, rmax_mult * tb);
-    int done = 0;
-    while (done < rows) {
-        const int rem = rows - done;
-        int r = (int)((double)rem * ns / (k * NW));  // remaining work ~ k tiles per warp
-        r = std::max(rmin, std::min(rmax, r));
-        // a tile reads r + 2*TB rows in stages of kRowsPerStage: make that a whole number of stages
+// Chunks of `r` rows (the last one takes the remainder, so r <= its height < 2r); every chunk holds >= G rows.
+// r + 2*TB is made a whole number of TMA stages, so a tile neither loads nor pushes rows it does not need.
+void fill_geometry(int rows, int own_lo, int G, int tb, int r, Geometry* g) {
+    r = std::max(std::max(r, G), 1);
+    if (r < rows) {
         r -= (r + 2 * tb) % kRowsPerStage;
-        if (r < rmin) r += kRowsPerStage;
-        if (rem - r < rmin) r = rem;  // no sliver at the end (every chunk >= ghost depth)
-        if ((int)y.size() >= kMaxChunks) r = rem;
-        done += r;
-        y.push_back(own_lo + done);
+        while (r < G) r += kRowsPerStage;
     }
+    int nc = std::max(1, rows / r);
+    if (nc > kMaxChunks) {
+        nc = kMaxChunks;
+        r = rows / nc;
+    }
+    g->chunk_r = r;
+    g->chunk_y.clear();
+    for (int c = 0; c <= nc; ++c) g->chunk_y.push_back(chunk_row_of(own_lo, rows, nc, r, c));
 }
 
-void build_chunks(const mcp_fused2d_plan* pl, int tb, std::vector<int>* out, int* n_strips) {
-    const mcp_fused2d_desc& d = pl->d;
-    const int outw = outw_rt(d.dtype, tb);
-    const int ns = (int)ceil_div(d.w, outw);
+// Tile height.  Two overheads pull in opposite directions: every tile re-reads and partly recomputes 2*TB pre-roll rows
+// and refills its TMA pipeline (~(TB + 6) row-times per tile), and a sweep ends with about half a tile of idle time
+// per warp.  With `share` rows of work per warp, overhead(r) ~ (TB + 6)/r + r/(2*share) is minimal at
+// r* = sqrt(2*share*(TB + 6)).
+int formula_rows(const mcp_fused2d_desc& d, int grid, int tb, int ns) {
+    const int NW = grid * warps_for(op_kind(d), tb);
+    const double share = (double)d.rows_own * ns / NW;
+    return (int)std::lround(std::sqrt(2.0 * share * (tb + 6)));
+}
+
+// Schedule for the grid-barrier path: one chunk = one tile.
+void build_barrier_geometry(const mcp_fused2d_desc& d, int grid, int tb, Geometry* g) {
+    const int ns = (int)ceil_div(d.w, outw_rt(d.dtype, tb));
     const int G = std::max(d.ghost, 1);
-    const int own_lo = d.ghost;
-    const int rows = d.rows_own;
-    *n_strips = ns;
-    std::vector<int>& y = *out;
-    if (d.chunk_rows > 0) {
-        y.clear();
-        y.push_back(own_lo);
-        const int nc = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(ceil_div(rows, d.chunk_rows),
-                                                                                   std::max(1, rows / G)), kMaxChunks));
-        for (int c = 1; c <= nc; ++c) y.push_back(own_lo + (int)((long long)rows * c / nc));
-        return;
-    }
-    const int NW = pl->grid * warps_for(op_kind(d), tb);
-    const char* e_k = getenv("MCP_GSS_K");
-    const char* e_rmin = getenv("MCP_GSS_RMIN");
-    const char* e_rmax = getenv("MCP_GSS_RMAX");
-    if (e_k || e_rmin || e_rmax) {  // manual override for experiments
-        gss_chunks(rows, own_lo, ns, NW, tb, G, e_k ? atof(e_k) : 3.0, e_rmin ? atoi(e_rmin) : 8,
-                   e_rmax ? atoi(e_rmax) : 48, &y);
-        return;
-    }
-    // Two overheads pull in opposite directions: every chunk re-reads and partly recomputes 2*TB pre-roll rows and
-    // refills its TMA pipeline (~(TB + 6) row-times per tile), and the sweep ends with about half a tile of idle
-    // time per warp.  With `share` rows of work per warp, overhead(r) ~ (TB + 6)/r + r/(2*share) is minimal at
-    // r* = sqrt(2*share*(TB + 6)); the measured optimum on B200 follows this within noise (profiles/).
-    const double share = (double)rows * ns / NW;
-    const int rmin = std::max(G, 4 * tb);
-    int r = (int)std::lround(std::sqrt(2.0 * share * (tb + 6)));
-    r = std::max(rmin, std::min(64 * tb, r));
-    r -= (r + 2 * tb) % kRowsPerStage;  // whole number of TMA stages per tile
-    if (r < rmin) r += kRowsPerStage;
-    y.clear();
-    y.push_back(own_lo);
-    int done = 0;
-    while (done < rows) {
-        int take = std::min(r, rows - done);
-        if (rows - done - take < rmin) take = rows - done;  // fold a sliver into the last chunk
-        if ((int)y.size() >= kMaxChunks) take = rows - done;
-        done += take;
-        y.push_back(own_lo + done);
-    }
+    g->n_strips = ns;
+    int r = d.chunk_rows;
+    if (r <= 0) r = std::max(std::max(G, 4 * tb), std::min(64 * tb, formula_rows(d, grid, tb, ns)));
+    fill_geometry(d.rows_own, d.ghost, G, tb, r, g);
 }
 
-void choose_geometry(const mcp_fused2d_plan* pl, int tb, int* n_strips, int* n_chunks) {
-    const std::vector<int>& y = pl->chunk_host[tb_index(tb)];
-    *n_strips = (int)ceil_div(pl->d.w, outw_rt(pl->d.dtype, tb));
-    *n_chunks = (int)y.size() - 1;
+// Schedule for the barrier-free path: a tile waits for its nine neighbours of the previous sweep and publishes itself.
+void build_dataflow_geometry(const mcp_fused2d_desc& d, int grid, int tb, Geometry* g) {
+    const int ns = (int)ceil_div(d.w, outw_rt(d.dtype, tb));
+    const int G = std::max(d.ghost, 1), rows = d.rows_own;
+    g->n_strips = ns;
+    int r = d.chunk_rows;
+    // measured on B200 (profiles/): never below 16 time blocks -- a tile pays ~2 us of TMA refill and a publish on top
+    // of the pre-roll, which short tiles cannot amortise
+    if (r <= 0) r = std::max(16 * tb, std::min(64 * tb, formula_rows(d, grid, tb, ns)));
+    fill_geometry(rows, d.ghost, G, tb, r, g);
+}
+
+void build_geometry(const mcp_fused2d_desc& d, int grid, int tb, int mode, Geometry* g) {
+    if (mode == 0)
+        build_barrier_geometry(d, grid, tb, g);
+    else
+        build_dataflow_geometry(d, grid, tb, g);
 }
 
 template <class Op, int TB>
-int launch_variant(mcp_fused2d_plan* pl, const Fused2dParams& p, bool res, cudaStream_t stream) {
-    constexpr int W = warps_for(std::is_same<Op, LifeB1>::value ? 2 : (std::is_same<Op, LifeI32>::value ? 1 : 0), TB);
-    constexpr int smem = smem_bytes_for(W);
-    void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
-    const void* fn = res ? (const void*)fused2d_kernel<Op, TB, true, W> : (const void*)fused2d_kernel<Op, TB, false, W>;
-    MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(pl->grid), dim3(W * 32), args, smem, stream));
-    pl->launches++;
-    return MCP_OK;
+const void* kernel_ptr(bool res, bool group) {
+    constexpr int W = warps_for(std::is_same<Op, LifeB1>::value ? 2 : std::is_same<Op, LifeI32>::value ? 1 : std::is_same<Op, MdfF64>::value ? 3 : 0, TB);
+    if (group) {
+        if constexpr (std::is_same<Op, MdfF32>::value && (TB == 4 || TB == 8)) {
+            return res ? (const void*)fused2d_group_kernel<Op, TB, true, W> : (const void*)fused2d_group_kernel<Op, TB, false, W>;
+        } else {
+            return nullptr;
+        }
+    }
+    return res ? (const void*)fused2d_kernel<Op, TB, true, W> : (const void*)fused2d_kernel<Op, TB, false, W>;
+}
+
+template <class Op, int TB>
+constexpr int kernel_warps() {
+    return warps_for(std::is_same<Op, LifeB1>::value ? 2 : std::is_same<Op, LifeI32>::value ? 1 : std::is_same<Op, MdfF64>::value ? 3 : 0, TB);
 }
 
 template <class Op>
-int launch_tb(mcp_fused2d_plan* pl, int tb, const Fused2dParams& p, bool res, cudaStream_t stream) {
+int pick_tb(int tb, bool res, bool group, const void** fn, int* warps) {
     switch (tb) {
-        case 1: return launch_variant<Op, 1>(pl, p, res, stream);
-        case 2: return launch_variant<Op, 2>(pl, p, res, stream);
-        case 4: return launch_variant<Op, 4>(pl, p, res, stream);
+        case 1: *fn = kernel_ptr<Op, 1>(res, group); *warps = kernel_warps<Op, 1>(); return MCP_OK;
+        case 2: *fn = kernel_ptr<Op, 2>(res, group); *warps = kernel_warps<Op, 2>(); return MCP_OK;
+        case 4: *fn = kernel_ptr<Op, 4>(res, group); *warps = kernel_warps<Op, 4>(); return MCP_OK;
         default: break;
     }
     set_error("unsupported time block %d", tb);
     return MCP_ERR_UNSUPPORTED;
 }
 
-int launch_any(mcp_fused2d_plan* pl, int tb, const Fused2dParams& p, bool res, cudaStream_t stream) {
-    const mcp_fused2d_desc& d = pl->d;
+int pick_kernel(const mcp_fused2d_desc& d, int tb, bool res, bool group, const void** fn, int* warps) {
     if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F32) {
-        if (tb == 8) return launch_variant<MdfF32, 8>(pl, p, res, stream);
-        return launch_tb<MdfF32>(pl, tb, p, res, stream);
+        if (tb == 8) { *fn = kernel_ptr<MdfF32, 8>(res, group); *warps = kernel_warps<MdfF32, 8>(); return MCP_OK; }
+        return pick_tb<MdfF32>(tb, res, group, fn, warps);
     }
     if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F64) {
-        if (tb == 8) return launch_variant<MdfF64, 8>(pl, p, res, stream);
-        return launch_tb<MdfF64>(pl, tb, p, res, stream);
+        if (tb == 8) { *fn = kernel_ptr<MdfF64, 8>(res, group); *warps = kernel_warps<MdfF64, 8>(); return MCP_OK; }
+        return pick_tb<MdfF64>(tb, res, group, fn, warps);
     }
-    if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_I32) return launch_tb<LifeI32>(pl, tb, p, res, stream);
-    if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_B1) return launch_tb<LifeB1>(pl, tb, p, res, stream);
+    if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_I32) return pick_tb<LifeI32>(tb, res, group, fn, warps);
+    if (d.op == MCP_OP_LIFE && d.dtype == MCP_DTYPE_B1) return pick_tb<LifeB1>(tb, res, group, fn, warps);
     set_error("unsupported op/dtype combination %d/%d", d.op, d.dtype);
     return MCP_ERR_UNSUPPORTED;
+}
+
+// What one launch does, decided on the host before the kernel parameters are filled in.
+struct LaunchSpec {
+    int tb, sweeps, mode;  // mode: 0 = grid barrier, 1 = dataflow
+    bool res;              // residual instantiation of the kernel
+    int res_first_sweep;
+    int stop_mode;
+    double stop_thresh;
+};
+
+int fill_params(mcp_fused2d_plan* pl, const LaunchSpec& ls, Fused2dParams* out) {
+    const mcp_fused2d_desc& d = pl->d;
+    const Geometry& g = pl->geo[tb_index(ls.tb)][ls.mode];
+    const int ns = g.n_strips;
+    MCP_REQUIRE((size_t)ns * g.n_chunks() <= pl->partials_cap_tiles, "tile count %d x %d exceeds scratch capacity", ns,
+                g.n_chunks());
+    const bool exchange = d.world > 1 && (d.res_inbox != nullptr || d.nvls_mc != nullptr);
+    Fused2dParams& p = *out;
+    memset(&p, 0, sizeof(p));
+    for (int b = 0; b < 2; ++b) {
+        p.buf[b] = d.buf[b];
+        p.up_buf[b] = d.up_buf[b];
+        p.dn_buf[b] = d.dn_buf[b];
+    }
+    p.my_flags = (const unsigned long long*)d.flags;
+    p.up_flag = (unsigned long long*)d.up_flag;
+    p.dn_flag = (unsigned long long*)d.dn_flag;
+    p.grid_bar = pl->grid_bar;
+    p.tile_ctr = pl->grid_bar + 16;  // separate 128-byte lines of the same zeroed allocation
+    p.res_count = reinterpret_cast<unsigned*>(pl->grid_bar + 32);
+    p.ctr_base = pl->ctr_base;
+    p.tile_done = pl->tile_done;
+    p.tile_ns = pl->tile_ns;
+    pl->last_tiles = ns * g.n_chunks();
+    p.result = pl->result;
+    p.status = &pl->result->status;
+    p.stop_word = &pl->result->stop_word;
+    p.partials = pl->partials;
+    p.res_out = pl->res_out;
+    p.flag_base_up = pl->flag_base_up;
+    p.flag_base_dn = pl->flag_base_dn;
+    p.bar_base = pl->bar_base;
+    p.timeout_ns = pl->timeout_ns;
+    p.pitch = d.pitch;
+    p.rows_alloc = pl->rows_alloc;
+    p.h = d.h;
+    p.w = d.w;
+    p.row0 = d.row_start - d.ghost;
+    p.own_lo = d.ghost;
+    p.own_hi = d.ghost + d.rows_own;
+    p.ylo = d.ylo; p.yhi = d.yhi; p.xlo = d.xlo; p.xhi = d.xhi;
+    p.G = d.ghost;
+    p.up_ghost_row = d.ghost + d.up_rows_own;
+    p.n_strips = ns;
+    p.n_chunks = g.n_chunks();
+    p.chunk_r = g.chunk_r;
+    p.sweeps = ls.sweeps;
+    p.first_parity = pl->parity;
+    p.res_slot0 = pl->res_slots_used;
+    p.res_first_sweep = ls.res ? ls.res_first_sweep : ls.sweeps;
+    p.debug_flags = pl->debug_flags;
+    p.world = d.world > 0 ? d.world : 1;
+    p.rank = d.rank;
+    p.res_flag = (const unsigned long long*)d.res_flag;
+    p.res_seq_base = pl->res_seq;
+    if (exchange)
+        for (int r = 0; r < p.world; ++r) {
+            p.peer_inbox[r] = (double*)d.peer_res_inbox[r];
+            p.peer_res_flag[r] = (unsigned long long*)d.peer_res_flag[r];
+        }
+    p.strip_flags = (const unsigned long long*)d.strip_flags;
+    p.up_strip_flag = (unsigned long long*)d.up_strip_flag;
+    p.dn_strip_flag = (unsigned long long*)d.dn_strip_flag;
+    p.seq_base = pl->sweep_seq;
+    p.prev_n_strips = pl->last_ns;
+    p.nvls_local = (unsigned char*)d.nvls_local;
+    p.nvls_mc = (unsigned char*)d.nvls_mc;
+    p.stop_mode = ls.stop_mode;
+    p.stop_thresh = ls.stop_thresh;
+    p.sync_mode = ls.mode == 0 ? 1 : 2;
+    return MCP_OK;
+}
+
+// Host bookkeeping after a launch that executed `executed` sweeps (all counters are monotonic across launches).
+void account(mcp_fused2d_plan* pl, const LaunchSpec& ls, int executed, int warps) {
+    const mcp_fused2d_desc& d = pl->d;
+    const Geometry& g = pl->geo[tb_index(ls.tb)][ls.mode];
+    const unsigned long long tiles = (unsigned long long)g.n_strips * g.n_chunks();
+    const unsigned long long nw = (unsigned long long)pl->grid * warps;
+    const int res_sweeps = ls.res ? std::max(0, executed - ls.res_first_sweep) : 0;
+    if (ls.mode == 0) {
+        // a barrier after every sweep but the last, and after the last one too when it carries the residual
+        unsigned long long barriers = (unsigned long long)std::max(0, executed - 1);
+        if (executed > 0 && ls.res && executed - 1 >= ls.res_first_sweep) barriers += 1;
+        pl->bar_base += barriers * (unsigned long long)pl->grid;
+        pl->ctr_base += (unsigned long long)executed * (tiles + nw);
+    } else {
+        pl->ctr_base += (unsigned long long)executed * tiles + nw;
+    }
+    pl->flag_base_up += (unsigned long long)executed * g.n_strips;
+    pl->flag_base_dn += (unsigned long long)executed * g.n_strips;
+    pl->parity = (pl->parity + executed) & 1;
+    pl->sweep_seq += (unsigned long long)executed;
+    pl->last_ns = g.n_strips;
+    if (ls.res) {
+        pl->res_slots_used = std::min(kMaxResSlots, pl->res_slots_used + res_sweeps);
+        const bool exchange = d.world > 1 && (d.res_inbox != nullptr || d.nvls_mc != nullptr);
+        if (exchange) pl->res_seq += (unsigned long long)res_sweeps;
+    }
+    pl->last_generations += executed * ls.tb;
+}
+
+int choose_mode(const mcp_fused2d_plan* pl, bool every_sweep_residual) {
+    if (every_sweep_residual) return 0;  // CTA 0 reduces a finished sweep behind the grid barrier
+    if (pl->sync_mode == 1) return 0;
+    return 1;
 }
 
 }  // namespace
 
 extern "C" {
+
+int mcp_fused2d_destroy(mcp_fused2d_plan* pl);
 
 int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out) {
     MCP_REQUIRE(desc && plan_out, "mcp_fused2d_create: null argument");
@@ -1044,6 +1066,7 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         MCP_REQUIRE(!d.dn_buf[0] || d.dn_strip_flag, "dn_strip_flag required with strip_flags and dn_buf");
         MCP_REQUIRE(ceil_div(d.w, outw_rt(d.dtype, 1)) <= kMaxStripFlags, "grid too wide for per-strip halo flags");
     }
+    MCP_REQUIRE(d.chunk_rows >= 0, "negative chunk_rows");
 
     mcp_fused2d_plan* pl = new (std::nothrow) mcp_fused2d_plan();
     MCP_REQUIRE(pl, "out of host memory");
@@ -1054,21 +1077,21 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->res_slots_used = 0;
     pl->launches = 0;
     pl->timeout_ns = 20ull * 1000000000ull;
-    pl->debug_flags = getenv("MCP_DEBUG_FLAGS") ? atoi(getenv("MCP_DEBUG_FLAGS")) : 0;
-    pl->sync_mode = getenv("MCP_SYNC_MODE") ? atoi(getenv("MCP_SYNC_MODE")) : 0;
+    pl->debug_flags = 0;
+    pl->sync_mode = 0;
     pl->grid_bar = nullptr;
-    pl->status = nullptr;
+    pl->result = nullptr;
     pl->partials = nullptr;
     pl->res_out = nullptr;
-    pl->chunk_tab = nullptr;
-    pl->stop_words = nullptr;
     pl->tile_done = nullptr;
     pl->tile_ns = nullptr;
+    pl->group_args = nullptr;
     pl->last_tiles = 0;
     pl->res_seq = 0;
     pl->sweep_seq = 0;
     pl->last_ns = 0;
     pl->last_generations = 0;
+    pl->last_stop_reason = MCP_STOP_NONE;
 
     int rc = device_sm_count(&pl->sm_count);
     if (rc) { delete pl; return rc; }
@@ -1084,196 +1107,137 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
                                strides, box);
         if (rc) { delete pl; return rc; }
     }
-    // scratch: grid barrier counter, status word, residual partials + history
+    // scratch: counters, result block, residual partials + history, per-chunk flags, schedule tables
     const int min_outw = outw_rt(d.dtype, max_tb(d.op, d.dtype));
     const size_t max_strips = (size_t)ceil_div(d.w, min_outw);
     const size_t max_chunks = (size_t)std::max(1, d.rows_own / std::max(d.ghost, 1));
-    pl->partials_cap_tiles = max_strips * std::min<size_t>(max_chunks, 4096);
+    pl->partials_cap_tiles = max_strips * std::min<size_t>(max_chunks, kMaxChunks);
     cudaError_t e;
-    if ((e = cudaMalloc(&pl->grid_bar, 256)) != cudaSuccess || (e = cudaMemset(pl->grid_bar, 0, 256)) != cudaSuccess ||
-        (e = cudaMalloc(&pl->status, 256)) != cudaSuccess || (e = cudaMemset(pl->status, 0, 256)) != cudaSuccess ||
+    if ((e = cudaMalloc(&pl->grid_bar, 512)) != cudaSuccess || (e = cudaMemset(pl->grid_bar, 0, 512)) != cudaSuccess ||
+        (e = cudaMalloc(&pl->result, 256)) != cudaSuccess || (e = cudaMemset(pl->result, 0, 256)) != cudaSuccess ||
         (e = cudaMalloc(&pl->partials, pl->partials_cap_tiles * 4 * sizeof(double))) != cudaSuccess ||
         (e = cudaMalloc(&pl->res_out, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
-        (e = cudaMemset(pl->res_out, 0, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess) {
+        (e = cudaMemset(pl->res_out, 0, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
+        (e = cudaMalloc(&pl->tile_ns, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
+        (e = cudaMemset(pl->tile_ns, 0, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
+        (e = cudaMalloc(&pl->tile_done, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess) {
         set_error("mcp_fused2d_create: scratch allocation failed: %s", cudaGetErrorString(e));
         mcp_fused2d_destroy(pl);
         return MCP_ERR_CUDA;
     }
-    if ((e = cudaMalloc(&pl->stop_words, 256)) != cudaSuccess || (e = cudaMemset(pl->stop_words, 0, 256)) != cudaSuccess) {
-        set_error("mcp_fused2d_create: stop word allocation failed: %s", cudaGetErrorString(e));
-        mcp_fused2d_destroy(pl);
-        return MCP_ERR_CUDA;
-    }
-    if ((e = cudaMalloc(&pl->tile_ns, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
-        (e = cudaMemset(pl->tile_ns, 0, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
-        (e = cudaMalloc(&pl->tile_done, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess) {
-        set_error("mcp_fused2d_create: tile flag allocation failed: %s", cudaGetErrorString(e));
-        mcp_fused2d_destroy(pl);
-        return MCP_ERR_CUDA;
-    }
-    if ((e = cudaMalloc(&pl->chunk_tab, 4 * (kMaxChunks + 1) * sizeof(int))) != cudaSuccess) {
-        set_error("mcp_fused2d_create: chunk table allocation failed: %s", cudaGetErrorString(e));
-        mcp_fused2d_destroy(pl);
-        return MCP_ERR_CUDA;
-    }
-    for (int tb = 1; tb <= 8; tb *= 2) {
-        int ns = 0;
-        std::vector<int>& y = pl->chunk_host[tb_index(tb)];
-        build_chunks(pl, tb, &y, &ns);
-        e = cudaMemcpy(pl->chunk_tab + tb_index(tb) * (kMaxChunks + 1), y.data(), y.size() * sizeof(int),
-                       cudaMemcpyHostToDevice);
-        if (e != cudaSuccess) {
-            set_error("mcp_fused2d_create: chunk table upload failed: %s", cudaGetErrorString(e));
-            mcp_fused2d_destroy(pl);
-            return MCP_ERR_CUDA;
-        }
-    }
+    for (int tb = 1; tb <= 8; tb *= 2)
+        for (int mode = 0; mode < 2; ++mode) build_geometry(d, pl->grid, tb, mode, &pl->geo[tb_index(tb)][mode]);
     *plan_out = pl;
     return MCP_OK;
+}
+
+int mcp_fused2d_set_option(mcp_fused2d_plan* pl, int option, long long value) {
+    MCP_REQUIRE(pl, "null plan");
+    switch (option) {
+        case MCP_OPT_TIMEOUT_MS:
+            MCP_REQUIRE(value >= 1, "timeout must be >= 1 ms");
+            pl->timeout_ns = (unsigned long long)value * 1000000ull;
+            return MCP_OK;
+        case MCP_OPT_DEBUG_FLAGS:
+            pl->debug_flags = (int)value;
+            return MCP_OK;
+        case MCP_OPT_SYNC_MODE:
+            MCP_REQUIRE(value >= 0 && value <= 2, "sync mode must be 0 (choose), 1 (grid barrier) or 2 (dataflow)");
+            pl->sync_mode = (int)value;
+            return MCP_OK;
+        default: break;
+    }
+    set_error("unknown option %d", option);
+    return MCP_ERR_ARG;
 }
 
 int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_strips, int* n_chunks, int* grid,
                          int* smem_bytes) {
     MCP_REQUIRE(pl, "null plan");
-    int ns, nc;
-    choose_geometry(pl, time_block, &ns, &nc);
-    if (n_strips) *n_strips = ns;
-    if (n_chunks) *n_chunks = nc;
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    if (n_strips) *n_strips = g.n_strips;
+    if (n_chunks) *n_chunks = g.n_chunks();
     if (grid) *grid = pl->grid;
     if (smem_bytes) *smem_bytes = smem_bytes_for(warps_for(op_kind(pl->d), time_block));
     return MCP_OK;
 }
 
+// Heights of the row chunks (= tiles) of the default schedule, in slab order.
 int mcp_fused2d_chunks(const mcp_fused2d_plan* pl, int time_block, int* rows_out, int max_entries) {
     MCP_REQUIRE(pl && rows_out, "null argument");
-    const std::vector<int>& y = pl->chunk_host[tb_index(time_block)];
-    const int n = std::min((int)y.size() - 1, max_entries);
-    for (int i = 0; i < n; ++i) rows_out[i] = y[i + 1] - y[i];
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const int n = std::min(g.n_chunks(), max_entries);
+    for (int i = 0; i < n; ++i) rows_out[i] = g.chunk_y[i + 1] - g.chunk_y[i];
     return n;
 }
 
-static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, bool res, int stop_mode,
+static int launch(mcp_fused2d_plan* pl, const LaunchSpec& ls, cudaStream_t stream, int* warps_out) {
+    Fused2dParams p;
+    int rc = fill_params(pl, ls, &p);
+    if (rc) return rc;
+    const void* fn = nullptr;
+    int warps = 0;
+    rc = pick_kernel(pl->d, ls.tb, ls.res, false, &fn, &warps);
+    if (rc) return rc;
+    if (ls.stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(&pl->result->stop_word, 0, 2 * sizeof(int), stream));
+    if (ls.mode == 1)
+        MCP_CUDA_TRY(cudaMemsetAsync(pl->tile_done, 0, (size_t)p.n_strips * p.n_chunks * sizeof(unsigned), stream));
+    const int smem = smem_bytes_for(warps);
+    void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
+    MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(pl->grid), dim3(warps * 32), args, smem, stream));
+    pl->launches++;
+    *warps_out = warps;
+    return MCP_OK;
+}
+
+static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, int residual_mode, int stop_mode,
                     double stop_thresh, cudaStream_t stream) {
     const mcp_fused2d_desc& d = pl->d;
     const int tbmax = std::min(max_tb(d.op, d.dtype), d.ghost);
     int tb = 1;
     while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
-    if (res) pl->res_slots_used = 0;
+    if (residual_mode != MCP_RES_NONE) pl->res_slots_used = 0;
     pl->last_generations = 0;
-    const bool exchange = d.world > 1 && (d.res_inbox != nullptr || d.nvls_mc != nullptr);
+    pl->last_stop_reason = MCP_STOP_NONE;
 
     int remaining = generations;
     while (remaining > 0) {
         while (tb > remaining) tb >>= 1;
-        const int sweeps = remaining / tb;
-        int ns, nc;
-        choose_geometry(pl, tb, &ns, &nc);
-        MCP_REQUIRE((size_t)ns * nc <= pl->partials_cap_tiles, "tile count %d x %d exceeds scratch capacity", ns, nc);
+        LaunchSpec ls;
+        ls.tb = tb;
+        ls.sweeps = remaining / tb;
+        const bool last_launch = remaining - ls.sweeps * tb == 0;
+        // MCP_RES_LAST: every sweep carries the residual; MCP_RES_FINAL: only the very last sweep of the run
+        ls.res = residual_mode == MCP_RES_LAST || (residual_mode == MCP_RES_FINAL && last_launch);
+        ls.res_first_sweep = residual_mode == MCP_RES_FINAL ? ls.sweeps - 1 : 0;
+        if (stop_mode != 0) ls.sweeps = std::min(ls.sweeps, kMaxResSlots);
+        ls.stop_mode = stop_mode;
+        ls.stop_thresh = stop_thresh;
+        ls.mode = choose_mode(pl, ls.res && ls.res_first_sweep < ls.sweeps - 1);
+        if (stop_mode != 0) ls.mode = 0;
 
-        Fused2dParams p;
-        memset(&p, 0, sizeof(p));
-        for (int b = 0; b < 2; ++b) {
-            p.buf[b] = d.buf[b];
-            p.up_buf[b] = d.up_buf[b];
-            p.dn_buf[b] = d.dn_buf[b];
-        }
-        p.my_flags = (const unsigned long long*)d.flags;
-        p.up_flag = (unsigned long long*)d.up_flag;
-        p.dn_flag = (unsigned long long*)d.dn_flag;
-        p.grid_bar = pl->grid_bar;
-        p.tile_ctr = pl->grid_bar + 16;  // separate 128-byte line of the same zeroed allocation
-        p.ctr_base = pl->ctr_base;
-        p.tile_done = pl->tile_done;
-        p.tile_ns = pl->tile_ns;
-        pl->last_tiles = ns * nc;
-        p.status = pl->status;
-        p.partials = pl->partials;
-        p.res_out = pl->res_out;
-        p.chunk_y = pl->chunk_tab + tb_index(tb) * (kMaxChunks + 1);
-        p.flag_base_up = pl->flag_base_up;
-        p.flag_base_dn = pl->flag_base_dn;
-        p.bar_base = pl->bar_base;
-        p.timeout_ns = pl->timeout_ns;
-        p.pitch = d.pitch;
-        p.rows_alloc = pl->rows_alloc;
-        p.h = d.h;
-        p.w = d.w;
-        p.row0 = d.row_start - d.ghost;
-        p.own_lo = d.ghost;
-        p.own_hi = d.ghost + d.rows_own;
-        p.ylo = d.ylo; p.yhi = d.yhi; p.xlo = d.xlo; p.xhi = d.xhi;
-        p.G = d.ghost;
-        p.up_ghost_row = d.ghost + d.up_rows_own;
-        p.n_strips = ns;
-        p.n_chunks = nc;
-        p.sweeps = sweeps;
-        p.first_parity = pl->parity;
-        p.res_slot0 = pl->res_slots_used;
-        p.debug_flags = pl->debug_flags;
-        p.world = d.world > 0 ? d.world : 1;
-        p.rank = d.rank;
-        p.res_flag = (const unsigned long long*)d.res_flag;
-        p.res_seq_base = pl->res_seq;
-        if (exchange)
-            for (int r = 0; r < p.world; ++r) {
-                p.peer_inbox[r] = (double*)d.peer_res_inbox[r];
-                p.peer_res_flag[r] = (unsigned long long*)d.peer_res_flag[r];
-            }
-        p.strip_flags = (const unsigned long long*)d.strip_flags;
-        p.up_strip_flag = (unsigned long long*)d.up_strip_flag;
-        p.dn_strip_flag = (unsigned long long*)d.dn_strip_flag;
-        p.seq_base = pl->sweep_seq;
-        p.prev_n_strips = pl->last_ns;
-        p.nvls_local = (unsigned char*)d.nvls_local;
-        p.nvls_mc = (unsigned char*)d.nvls_mc;
-        p.stop_word = pl->stop_words;
-        p.sweeps_done = pl->stop_words + 1;
-        p.stop_mode = stop_mode;
-        p.stop_thresh = stop_thresh;
-        if (stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(pl->stop_words, 0, 2 * sizeof(int), stream));
-        // Sweep synchronisation: per-tile dataflow flags remove the barrier and the idle tail of every sweep, which
-        // pays when a warp has few tiles per sweep; with many tiles per warp the plain barrier is cheaper.
-        int sync_mode = pl->sync_mode;
-        if (sync_mode == 0) {
-            const double tiles_per_warp = (double)ns * nc / ((double)pl->grid * warps_for(op_kind(d), tb));
-            sync_mode = (tb < 8 || tiles_per_warp < 5.0) ? 2 : 1;
-        }
-        if (res) sync_mode = 1;
-        p.sync_mode = sync_mode;
-        if (sync_mode == 2) MCP_CUDA_TRY(cudaMemsetAsync(pl->tile_done, 0, (size_t)ns * nc * sizeof(unsigned), stream));
-
-        int rc = launch_any(pl, tb, p, res, stream);
+        int warps = 0;
+        int rc = launch(pl, ls, stream, &warps);
         if (rc) return rc;
 
-        int executed = sweeps;
+        int executed = ls.sweeps;
         if (stop_mode != 0) {
             // the number of sweeps that ran is decided on the device: wait for it before touching the counters
             MCP_CUDA_TRY(cudaStreamSynchronize(stream));
-            int words[2] = {0, 0};
-            MCP_CUDA_TRY(cudaMemcpy(words, pl->stop_words, sizeof(words), cudaMemcpyDeviceToHost));
-            executed = words[1];
-            MCP_REQUIRE(executed >= 0 && executed <= sweeps, "device reported %d executed sweeps of %d", executed, sweeps);
+            ResultBlock rb;
+            MCP_CUDA_TRY(cudaMemcpy(&rb, pl->result, sizeof(rb), cudaMemcpyDeviceToHost));
+            executed = rb.sweeps_done;
+            MCP_REQUIRE(executed >= 0 && executed <= ls.sweeps, "device reported %d executed sweeps of %d", executed,
+                        ls.sweeps);
+            if (rb.stop_word != 0)
+                pl->last_stop_reason = MCP_STOP_CONVERGED;
+            else
+                pl->last_stop_reason = ls.sweeps < remaining / tb ? MCP_STOP_SLOT_LIMIT : MCP_STOP_MAX_GENERATIONS;
         }
-        const unsigned long long nw = (unsigned long long)pl->grid * warps_for(op_kind(d), tb);
-        if (sync_mode == 1) {
-            const unsigned long long barriers = res ? (unsigned long long)executed : (unsigned long long)(executed - 1);
-            pl->bar_base += barriers * (unsigned long long)pl->grid;
-            pl->ctr_base += (unsigned long long)executed * ((unsigned long long)ns * nc + nw);
-        } else {
-            pl->ctr_base += (unsigned long long)executed * ((unsigned long long)ns * nc) + nw;
-        }
-        pl->flag_base_up += (unsigned long long)executed * ns;
-        pl->flag_base_dn += (unsigned long long)executed * ns;
-        pl->parity = (pl->parity + executed) & 1;
-        pl->sweep_seq += (unsigned long long)executed;
-        pl->last_ns = ns;
-        if (res) {
-            pl->res_slots_used = std::min(kMaxResSlots, pl->res_slots_used + executed);
-            if (exchange) pl->res_seq += (unsigned long long)executed;
-        }
-        pl->last_generations += executed * tb;
+        account(pl, ls, executed, warps);
         if (stop_mode != 0) break;  // tolerance runs use one block size; the caller decides how to continue
-        remaining -= sweeps * tb;
+        remaining -= ls.sweeps * tb;
     }
     return MCP_OK;
 }
@@ -1282,7 +1246,9 @@ int mcp_fused2d_run(mcp_fused2d_plan* pl, int generations, int time_block, int r
     MCP_REQUIRE(pl, "null plan");
     MCP_REQUIRE(generations >= 0, "negative generation count");
     MCP_REQUIRE(time_block >= 1, "time_block must be >= 1");
-    return run_impl(pl, generations, time_block, residual_mode != MCP_RES_NONE, 0, 0.0, (cudaStream_t)stream_);
+    MCP_REQUIRE(residual_mode == MCP_RES_NONE || residual_mode == MCP_RES_LAST || residual_mode == MCP_RES_FINAL,
+                "residual_mode must be MCP_RES_NONE, MCP_RES_LAST or MCP_RES_FINAL");
+    return run_impl(pl, generations, time_block, residual_mode, 0, 0.0, (cudaStream_t)stream_);
 }
 
 int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int time_block, int norm, double tol,
@@ -1291,58 +1257,138 @@ int mcp_fused2d_run_to_tolerance(mcp_fused2d_plan* pl, int max_generations, int 
     MCP_REQUIRE(max_generations >= 1 && time_block >= 1, "bad generation count or time block");
     MCP_REQUIRE(norm == MCP_NORM_LINF || norm == MCP_NORM_L2, "norm must be MCP_NORM_LINF or MCP_NORM_L2");
     MCP_REQUIRE(tol >= 0.0, "negative tolerance");
+    const mcp_fused2d_desc& d = pl->d;
+    // Every rank must take the same stop decision in the same sweep, or the ranks that go on spin on halo flags
+    // that never come.  That needs the in-kernel all-reduce, and a reduction whose bits agree on every rank.
+    const bool neighbours = d.up_buf[0] != nullptr || d.dn_buf[0] != nullptr;
+    MCP_REQUIRE(!neighbours || d.res_inbox != nullptr || d.nvls_mc != nullptr,
+                "run_to_tolerance across ranks needs the fused residual exchange (res_inbox or nvls_mc): a local "
+                "residual would stop the ranks in different sweeps");
+    MCP_REQUIRE(!(neighbours && d.nvls_mc != nullptr && norm == MCP_NORM_L2),
+                "the NVLS sum is associated by the switch and may round differently per rank: use MCP_NORM_LINF with "
+                "nvls_mc, or the peer-inbox exchange for MCP_NORM_L2");
     const double thresh = norm == MCP_NORM_L2 ? tol * tol : tol;  // the kernel compares the sum of squares
-    int rc = run_impl(pl, max_generations, time_block, true, norm == MCP_NORM_LINF ? 1 : 2, thresh,
+    int rc = run_impl(pl, max_generations, time_block, MCP_RES_LAST, norm == MCP_NORM_LINF ? 1 : 2, thresh,
                       (cudaStream_t)stream_);
     if (generations_done) *generations_done = pl->last_generations;
     return rc;
 }
 
-// Queue position <-> (chunk, strip), the same functions the kernel uses (host build of decode_tile/encode_tile).
+int mcp_fused2d_stop_reason(const mcp_fused2d_plan* pl) { return pl ? pl->last_stop_reason : MCP_STOP_NONE; }
+
+// Emulated multi-rank launch: the plans of n ranks that live on THIS GPU advance together inside one cooperative
+// kernel (see fused2d_group_kernel).  One launch, fixed generation count, generations % time_block == 0.
+int mcp_fused2d_run_group(mcp_fused2d_plan** plans, int n, int generations, int time_block, int residual_mode,
+                          void* stream_) {
+    MCP_REQUIRE(plans && n >= 1 && n <= kMaxRanks, "bad plan list");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    mcp_fused2d_plan* p0 = plans[0];
+    MCP_REQUIRE(p0, "null plan");
+    const int tbmax = std::min(max_tb(p0->d.op, p0->d.dtype), p0->d.ghost);
+    int tb = 1;
+    while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
+    MCP_REQUIRE(generations >= tb && generations % tb == 0, "generations must be a positive multiple of the time block");
+    MCP_REQUIRE(residual_mode == MCP_RES_NONE || residual_mode == MCP_RES_LAST || residual_mode == MCP_RES_FINAL,
+                "bad residual mode");
+    const int ncta = p0->sm_count / n;
+    MCP_REQUIRE(ncta >= 1, "more ranks than SMs");
+    LaunchSpec ls;
+    ls.tb = tb;
+    ls.sweeps = generations / tb;
+    ls.res = residual_mode != MCP_RES_NONE;
+    ls.res_first_sweep = residual_mode == MCP_RES_FINAL ? ls.sweeps - 1 : 0;
+    ls.stop_mode = 0;
+    ls.stop_thresh = 0.0;
+    ls.mode = choose_mode(p0, ls.res && ls.res_first_sweep < ls.sweeps - 1);
+    const void* fn = nullptr;
+    int warps = 0;
+    int rc = pick_kernel(p0->d, tb, ls.res, true, &fn, &warps);
+    if (rc) return rc;
+    MCP_REQUIRE(fn != nullptr, "the emulated multi-rank launch is built for fp32 MDF with time block 4 or 8 only");
+    std::vector<GroupRankArgs> host((size_t)n);
+    for (int r = 0; r < n; ++r) {
+        mcp_fused2d_plan* pl = plans[r];
+        MCP_REQUIRE(pl && pl->d.op == p0->d.op && pl->d.dtype == p0->d.dtype && pl->d.ghost == p0->d.ghost,
+                    "plans of one group must share operator, dtype and ghost depth");
+        pl->grid = ncta;  // tile schedules and ticket accounting of this launch use the rank's share of the GPU
+        if (residual_mode != MCP_RES_NONE) pl->res_slots_used = 0;
+        pl->last_generations = 0;
+        rc = fill_params(pl, ls, &host[r].p);
+        if (rc) return rc;
+        host[r].tm[0] = pl->tm[0];
+        host[r].tm[1] = pl->tm[1];
+        if (ls.mode == 1)
+            MCP_CUDA_TRY(cudaMemsetAsync(pl->tile_done, 0,
+                                         (size_t)host[r].p.n_strips * host[r].p.n_chunks * sizeof(unsigned), stream));
+    }
+    if (p0->group_args == nullptr) MCP_CUDA_TRY(cudaMalloc(&p0->group_args, sizeof(GroupRankArgs) * kMaxRanks));
+    MCP_CUDA_TRY(cudaMemcpyAsync(p0->group_args, host.data(), sizeof(GroupRankArgs) * n, cudaMemcpyHostToDevice, stream));
+    MCP_CUDA_TRY(cudaStreamSynchronize(stream));  // `host` goes out of scope; the copy source must stay valid
+    const int smem = smem_bytes_for(warps);
+    const GroupRankArgs* dargs = p0->group_args;
+    int n_arg = n;
+    void* args[2] = {(void*)&dargs, (void*)&n_arg};
+    MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(ncta * n), dim3(warps * 32), args, smem, stream));
+    for (int r = 0; r < n; ++r) {
+        plans[r]->launches++;
+        account(plans[r], ls, ls.sweeps, warps);
+    }
+    return MCP_OK;
+}
+
+// Queue position <-> (group, strip), the same functions the kernel uses (host build of decode_tile/encode_tile).
 int mcp_fused2d_tile_at(int n_strips, int n_chunks, int q, int* chunk, int* strip) {
     MCP_REQUIRE(chunk && strip && n_strips >= 1 && n_chunks >= 1 && q >= 0 && q < n_strips * n_chunks, "bad arguments");
     decode_tile(q, n_strips, n_chunks, *chunk, *strip);
     return encode_tile(*chunk, *strip, n_strips, n_chunks);
 }
 
-// Device-free planning: the tile schedule a plan WOULD use (chunk heights in queue order, strip count) for a slab of
-// `rows_own` rows and `w` cells on `grid` CTAs.  Pure host arithmetic -- usable on a box without a GPU (tests).
-int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
-                              int chunk_rows, int* rows_out, int max_entries, int* n_strips) {
+// Device-free planning: the schedule a plan WOULD use for a slab of `rows_own` rows and `w` cells on `grid` CTAs --
+// chunk heights in slab order and the strip count.  mode 0 = grid-barrier schedule, 1 = barrier-free (dataflow)
+// schedule.  Pure host arithmetic (tests run it on a box without a GPU).  Returns the chunk count.
+int mcp_fused2d_plan_schedule2(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
+                               int chunk_rows, int mode, int* rows_out, int max_entries, int* n_strips) {
     MCP_REQUIRE(rows_out && n_strips, "null argument");
     MCP_REQUIRE(w >= 1 && rows_own >= 1 && ghost >= 1 && grid >= 1, "bad geometry");
     MCP_REQUIRE(time_block == 1 || time_block == 2 || time_block == 4 || time_block == 8, "time_block must be 1, 2, 4 or 8");
-    mcp_fused2d_plan tmp;
-    memset(&tmp.d, 0, sizeof(tmp.d));
-    tmp.d.op = op;
-    tmp.d.dtype = dtype;
-    tmp.d.w = w;
-    tmp.d.rows_own = rows_own;
-    tmp.d.ghost = ghost;
-    tmp.d.chunk_rows = chunk_rows;
-    tmp.grid = grid;
-    std::vector<int> y;
-    int ns = 0;
-    build_chunks(&tmp, time_block, &y, &ns);
-    *n_strips = ns;
-    const int n = std::min((int)y.size() - 1, max_entries);
-    for (int i = 0; i < n; ++i) rows_out[i] = y[i + 1] - y[i];
-    return (int)y.size() - 1;
+    MCP_REQUIRE(mode == 0 || mode == 1, "mode must be 0 or 1");
+    mcp_fused2d_desc d;
+    memset(&d, 0, sizeof(d));
+    d.op = op;
+    d.dtype = dtype;
+    d.w = w;
+    d.rows_own = rows_own;
+    d.ghost = ghost;
+    d.chunk_rows = chunk_rows;
+    Geometry g;
+    build_geometry(d, grid, time_block, mode, &g);
+    *n_strips = g.n_strips;
+    const int n = std::min(g.n_chunks(), max_entries);
+    for (int i = 0; i < n; ++i) rows_out[i] = g.chunk_y[i + 1] - g.chunk_y[i];
+    return g.n_chunks();
 }
 
-// Trace (MCP_DEBUG_FLAGS & 4): duration in ns of every tile in the last sweep it ran, in queue order, with its
-// (chunk, strip) so that a host tool can see which tiles are the critical path.
+int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
+                              int chunk_rows, int* rows_out, int max_entries, int* n_strips) {
+    return mcp_fused2d_plan_schedule2(op, dtype, w, rows_own, ghost, time_block, grid, chunk_rows, 0, rows_out,
+                                      max_entries, n_strips);
+}
+
+// Trace (MCP_OPT_DEBUG_FLAGS & 4): duration in ns of every tile in the last sweep it ran, in queue order, with its
+// (group, strip) so that a host tool can see which tiles are the critical path.
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* pl, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
                            int max_entries) {
     MCP_REQUIRE(pl && ns_out, "null argument");
-    int nstr, nch;
-    choose_geometry(pl, time_block, &nstr, &nch);
-    const int n = std::min(std::min(nstr * nch, pl->last_tiles), max_entries);
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const int nstr = g.n_strips, ng = g.n_chunks();
+    const int n = std::min(std::min(nstr * ng, pl->last_tiles), max_entries);
     if (n > 0) MCP_CUDA_TRY(cudaMemcpy(ns_out, pl->tile_ns, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     for (int q = 0; q < n; ++q) {
-        const int ci = q / nstr;
-        if (strip_out) strip_out[q] = q - ci * nstr;
-        if (chunk_out) chunk_out[q] = (ci & 1) ? nch - 1 - (ci >> 1) : (ci >> 1);
+        int group, strip;
+        decode_tile(q, nstr, ng, group, strip);
+        if (strip_out) strip_out[q] = strip;
+        if (chunk_out) chunk_out[q] = group;
     }
     return n;
 }
@@ -1375,12 +1421,29 @@ int mcp_fused2d_residuals(mcp_fused2d_plan* pl, double* out, int max_entries) {
     return n;
 }
 
+// One asynchronous 32-byte copy of the plan's result block (status, stop word, executed sweeps, last global
+// residual) into pinned host memory, ordered after the runs already enqueued on `stream`.
+int mcp_fused2d_result_async(mcp_fused2d_plan* pl, void* host32, void* stream_) {
+    MCP_REQUIRE(pl && host32, "null argument");
+    static_assert(sizeof(ResultBlock) == 32, "result block layout");
+    MCP_CUDA_TRY(cudaMemcpyAsync(host32, pl->result, sizeof(ResultBlock), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    return MCP_OK;
+}
+
 int mcp_fused2d_status(mcp_fused2d_plan* pl) {
     MCP_REQUIRE(pl, "null plan");
     int st = 0;
-    MCP_CUDA_TRY(cudaMemcpy(&st, pl->status, sizeof(int), cudaMemcpyDeviceToHost));
+    MCP_CUDA_TRY(cudaMemcpy(&st, &pl->result->status, sizeof(int), cudaMemcpyDeviceToHost));
     if (st != 0) set_error("fused2d kernel recorded status %d (%s)", st, st == MCP_ERR_TIMEOUT ? "flag/barrier wait timed out" : "error");
     return st;
+}
+
+// Clear a recorded kernel error (after a timeout the plan's counters no longer match the peers': destroy it, or
+// reset every rank's plan and flag pads together).
+int mcp_fused2d_clear_status(mcp_fused2d_plan* pl) {
+    MCP_REQUIRE(pl, "null plan");
+    MCP_CUDA_TRY(cudaMemset(&pl->result->status, 0, sizeof(int)));
+    return MCP_OK;
 }
 
 int64_t mcp_fused2d_launches(const mcp_fused2d_plan* pl) { return pl ? pl->launches : 0; }
@@ -1388,13 +1451,12 @@ int64_t mcp_fused2d_launches(const mcp_fused2d_plan* pl) { return pl ? pl->launc
 int mcp_fused2d_destroy(mcp_fused2d_plan* pl) {
     if (!pl) return MCP_OK;
     if (pl->grid_bar) cudaFree(pl->grid_bar);
-    if (pl->status) cudaFree(pl->status);
+    if (pl->result) cudaFree(pl->result);
     if (pl->partials) cudaFree(pl->partials);
     if (pl->res_out) cudaFree(pl->res_out);
-    if (pl->chunk_tab) cudaFree(pl->chunk_tab);
-    if (pl->stop_words) cudaFree(pl->stop_words);
     if (pl->tile_done) cudaFree(pl->tile_done);
     if (pl->tile_ns) cudaFree(pl->tile_ns);
+    if (pl->group_args) cudaFree(pl->group_args);
     delete pl;
     return MCP_OK;
 }

@@ -324,3 +324,22 @@ def run_field(cfg, u: np.ndarray, generations: int) -> np.ndarray:
     for _ in range(generations):
         u = step_field(cfg, u)
     return u
+
+
+def checksum_rows(rows: np.ndarray, grow0: int, w: int) -> int:
+    """NumPy restatement of ``mcp_checksum2d`` (ops/csrc/checksum.cu): wrapping sum over cells of
+    mix64(bit pattern ^ golden * global cell index)."""
+    a = np.ascontiguousarray(rows)
+    bits = a.view(np.uint64 if a.dtype.itemsize == 8 else np.uint32).astype(np.uint64)
+    h = a.shape[0]
+    with np.errstate(over="ignore"):
+        idx = (np.arange(h, dtype=np.uint64)[:, None] + np.uint64(grow0)) * np.uint64(w) + np.arange(w, dtype=np.uint64)[None, :]
+        z = bits ^ (idx * np.uint64(0x9E3779B97F4A7C15))
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+        return int(z.sum(dtype=np.uint64))
+
+
+def checksum_field(field: np.ndarray) -> int:
+    return checksum_rows(field, 0, field.shape[1])

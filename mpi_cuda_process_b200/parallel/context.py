@@ -96,6 +96,11 @@ def init_context(device: Optional[str] = None, backend: Optional[str] = None) ->
         raise RuntimeError("CUDA requested but no GPU is visible")
     if use_cuda:
         ndev = torch.cuda.device_count()
+        if local_rank >= ndev and os.environ.get("MCP_ALLOW_GPU_SHARING") != "1":
+            # Two ranks time-slicing one GPU cannot run the fused kernels: they are cooperative launches that fill
+            # every SM and spin on each other's flags (they would stall until the flag timeout).  One rank per GPU.
+            raise RuntimeError(f"LOCAL_RANK {local_rank} but only {ndev} GPU(s) visible: one rank per GPU is required "
+                               "(set MCP_ALLOW_GPU_SHARING=1 for the unfused baselines)")
         dev = torch.device("cuda", local_rank % max(ndev, 1))
         torch.cuda.set_device(dev)
     else:

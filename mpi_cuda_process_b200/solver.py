@@ -45,6 +45,7 @@ class RunStats:
     launches: int = 0
     halo_messages: int = 0
     residual_history: List[Tuple[int, float]] = field(default_factory=list)
+    stop_reason: str = ""           # run_to_tolerance: "converged" | "max_generations" | "slot_limit"
 
     @property
     def glups(self) -> float:
@@ -93,6 +94,7 @@ class Solver:
         self._closed = False
         self._ghosts_valid = True
         self._last_residual: Optional[Tuple[float, float]] = None
+        self.last_gather_stats: Optional[dict] = None
         self._scratch = None
         self._alloc()
 
@@ -268,6 +270,13 @@ class Solver:
         _lib.check(self._lib.mcp_fused2d_create(C.byref(d), C.byref(plan)), "mcp_fused2d_create")
         self._plan = plan
         self._desc = d
+        # plan options: explicit (cfg.extra), no environment lookups inside the native library
+        for key, opt in (("timeout_ms", 1), ("debug_flags", 2), ("sync_mode", 3)):
+            if cfg.extra.get(key) is not None:
+                _lib.check(self._lib.mcp_fused2d_set_option(plan, opt, int(cfg.extra[key])), "mcp_fused2d_set_option")
+        # one pinned 32-byte block for (status, stop word, sweeps done, last residual): read back with one async copy
+        self._result_host = torch.zeros(4, dtype=torch.float64).pin_memory()
+        self._result_event = torch.cuda.Event()
 
     # ------------------------------------------------------------------ initial condition
     def initialize(self, field: Optional[np.ndarray] = None) -> None:
@@ -366,8 +375,9 @@ class Solver:
         into the current buffer.  This is the public per-step input path timed by ``bench.py``'s e2e number."""
         if tuple(local.shape) != tuple(self.store_shape):
             raise ValueError(f"local shape {tuple(local.shape)} != {self.store_shape}")
-        if self.backend == "fused" and self.ctx.distributed:
-            # a neighbour's last halo push of the previous run may still be in flight towards our ghost rows
+        if self.backend == "fused" and self.ctx.distributed and self.ndim == 3:
+            # a neighbour's last halo push of the previous run may still be in flight towards our ghost layers
+            # (the 2-D kernel drains its incoming pushes before it ends, so stream order is enough there)
             self.ctx.barrier()
         self.bufs[self.cur].copy_(local, non_blocking=non_blocking)
         self._ghosts_valid = True
@@ -398,8 +408,10 @@ class Solver:
             self.bufs[self.cur].copy_(self._staged)
             self._ghosts_valid = True
             return
-        if self.backend == "fused" and self.ctx.distributed:
+        if self.backend == "fused" and self.ctx.distributed and self.ndim == 3:
             self.ctx.barrier()      # neighbours' last halo pushes of the previous run must have landed first
+        # 2-D fused: no host barrier -- before a sweep kernel ends it waits for the flags of every halo push the
+        # neighbours address to this rank (drain_incoming), so the copy below is ordered behind them by the stream
         cur = torch.cuda.current_stream(self.ctx.device)
         cur.wait_event(self._stage_done)
         self.bufs[self.cur].copy_(self._stage_buf, non_blocking=True)
@@ -420,6 +432,10 @@ class Solver:
         (every generation on the unfused backends); "final" = only the residual of the very last generation
         (the sweep kernel runs its cheaper residual-free instantiation for all but the last time block)."""
         g = self.cfg.generations if generations is None else int(generations)
+        self._res_final = False
+        if residual == "final" and self.backend == "fused" and self.ndim == 2:
+            self._res_final = True      # one launch: only the last time block runs the residual row loop
+            residual = True
         if residual == "final":
             tail = self.time_block if self.backend == "fused" else 1
             if g > tail:
@@ -489,12 +505,33 @@ class Solver:
         from .ops import _lib
         self._ensure_plan()
         before = self._lib.mcp_fused2d_launches(self._plan)
-        _lib.check(self._lib.mcp_fused2d_run(self._plan, g, self.time_block, 1 if residual else 0, self._stream()),
-                   "mcp_fused2d_run")
+        final = residual and getattr(self, "_res_final", False)
+        mode = 2 if final else (1 if residual else 0)
+        _lib.check(self._lib.mcp_fused2d_run(self._plan, g, self.time_block, mode, self._stream()), "mcp_fused2d_run")
         st.launches = int(self._lib.mcp_fused2d_launches(self._plan) - before)
         self.cur = self._lib.mcp_fused2d_parity(self._plan)
-        if residual:
+        if final and (self._res_in_kernel or not self.ctx.distributed):
+            self._collect_final_residual(st)
+        elif residual:
             self._collect_fused_residual(st)
+
+    def _collect_final_residual(self, st: RunStats) -> None:
+        """Status + global residual of the run's last generation: one asynchronous 32-byte copy into pinned memory
+        and one event, no blocking library call."""
+        from .ops import _lib
+        _lib.check(self._lib.mcp_fused2d_result_async(self._plan, self._result_host.data_ptr(), self._stream()),
+                   "mcp_fused2d_result_async")
+        self._result_event.record(torch.cuda.current_stream(self.ctx.device))
+        self._result_event.synchronize()
+        words = self._result_host.view(torch.int32)
+        status = int(words[0])
+        if status != 0:
+            raise _lib.NativeError(f"fused kernel recorded status {status}"
+                                   + (" (a flag / barrier / TMA wait timed out)" if status == -4 else ""))
+        ss, mx = float(self._result_host[2]), float(self._result_host[3])
+        self._last_residual = (ss, mx)
+        kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+        st.residual_history = [(-1, float(np.sqrt(ss)) if kind == "l2" else mx)]
 
     def _collect_fused_residual(self, st: RunStats) -> None:
         buf = (C.c_double * (2 * 16384))()
@@ -732,7 +769,15 @@ class Solver:
         total = RunStats(cells=self.cfg.cells)
         kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
         if self.backend == "fused" and self.ndim == 2 and not self.cfg.extra.get("host_tolerance_loop", False):
-            return self._run_to_tolerance_fused(tol, max_g, kind)
+            self._ensure_plan()
+            if self.ctx.distributed and self.cfg.extra.get("residual_allreduce") == "nvls" and kind == "l2":
+                raise ValueError("residual_allreduce='nvls' cannot drive an L2 stop rule: the switch's summation order "
+                                 "may round differently per rank and the ranks would stop in different sweeps; use "
+                                 "residual='linf' with NVLS or the default peer-to-peer exchange")
+            # the single-launch path needs a stop decision that is identical on every rank: only with the in-kernel
+            # all-reduce; otherwise fall through to the host loop (global residual through the control plane)
+            if not self.ctx.distributed or self._res_in_kernel:
+                return self._run_to_tolerance_fused(tol, max_g, kind)
         while total.generations < max_g:
             n = min(every, max_g - total.generations)
             if self.backend == "fused":
@@ -763,29 +808,36 @@ class Solver:
         return total
 
     def _run_to_tolerance_fused(self, tol: float, max_g: int, kind: str) -> RunStats:
-        """One launch: the kernel all-reduces the residual of every time block over NVLink and stops itself."""
+        """The kernel all-reduces the residual of every time block over NVLink and stops itself: one launch per 16384
+        time blocks (the size of the device-side residual history), normally one launch in all."""
         from .ops import _lib
         self._ensure_plan()
         tb = self.time_block
         max_g = max(tb, max_g // tb * tb)
-        max_g = min(max_g, 16384 * tb)
         st = RunStats(cells=self.cfg.cells)
-        done = C.c_int(0)
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        before = self._lib.mcp_fused2d_launches(self._plan)
-        ev0.record()
-        _lib.check(self._lib.mcp_fused2d_run_to_tolerance(self._plan, max_g, tb, 2 if kind == "l2" else 1, float(tol),
-                                                          C.byref(done), self._stream()),
-                   "mcp_fused2d_run_to_tolerance")
-        ev1.record()
-        ev1.synchronize()
-        st.device_ms = self.ctx.all_reduce_max(ev0.elapsed_time(ev1))
-        st.launches = int(self._lib.mcp_fused2d_launches(self._plan) - before)
-        st.generations = int(done.value)
-        self.cur = self._lib.mcp_fused2d_parity(self._plan)
-        base = self.generation
-        self._collect_fused_residual(st)
-        st.residual_history = [(base + (i + 1) * tb, r) for i, (_, r) in enumerate(st.residual_history)]
+        while True:
+            done = C.c_int(0)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            before = self._lib.mcp_fused2d_launches(self._plan)
+            ev0.record()
+            _lib.check(self._lib.mcp_fused2d_run_to_tolerance(self._plan, max_g - st.generations, tb,
+                                                              2 if kind == "l2" else 1, float(tol), C.byref(done),
+                                                              self._stream()), "mcp_fused2d_run_to_tolerance")
+            ev1.record()
+            ev1.synchronize()
+            st.device_ms += self.ctx.all_reduce_max(ev0.elapsed_time(ev1))
+            st.launches += int(self._lib.mcp_fused2d_launches(self._plan) - before)
+            self.cur = self._lib.mcp_fused2d_parity(self._plan)
+            part = RunStats()
+            self._collect_fused_residual(part)
+            base = self.generation + st.generations
+            st.residual_history += [(base + (i + 1) * tb, r) for i, (_, r) in enumerate(part.residual_history)]
+            st.generations += int(done.value)
+            st.stop_reason = {1: "converged", 2: "max_generations", 3: "slot_limit"}.get(
+                int(self._lib.mcp_fused2d_stop_reason(self._plan)), "")
+            # "slot_limit": the history table filled up before the tolerance was met -- not converged, go on
+            if st.stop_reason != "slot_limit" or st.generations >= max_g or done.value <= 0:
+                break
         self.generation += st.generations
         self.total_stats.generations += st.generations
         self.total_stats.device_ms += st.device_ms
@@ -810,19 +862,18 @@ class Solver:
         sl = tuple(slice(G, G + n) for n in self.own_shape[:-1]) + (slice(0, self.cfg.width),)
         return self.bufs[self.cur][sl]
 
-    def gather(self, as_fp32: bool = False) -> Optional[np.ndarray]:
+    def gather(self, as_fp32: bool = False, copy: bool = True) -> Optional[np.ndarray]:
         """Assemble the global field on rank 0 (None elsewhere).
 
-        On GPUs this is the fused gather + pack: every rank's pack kernel strips ghosts and pad (and optionally
-        casts fp64 -> fp32) while storing its block straight into rank 0's output buffer over NVLink; no
-        intermediate copies, no NCCL.  The reference has no gather: every rank holds (a stale copy of) the whole
-        grid (MDF_kernel.cu:137-144)."""
-        if self.ctx.is_cuda and not self.bits:
-            return self._gather_p2p(as_fp32)
-        loc = self.local_owned()
+        On GPUs this is the fused gather + pack: every rank's pack kernel strips ghosts and pad (optionally casts
+        fp64 -> fp32, or unpacks bit-packed life cells) while storing its block straight into rank 0's output buffer
+        over NVLink in 16-byte vectors; no intermediate copies, no NCCL.  Rank 0 then copies the dense field into a
+        pinned host buffer.  ``copy=False`` returns a view of that pinned buffer (valid until the next gather) instead
+        of a private array.  The reference has no gather: every rank holds (a stale copy of) the whole grid
+        (MDF_kernel.cu:137-144)."""
         if self.ctx.is_cuda:
-            torch.cuda.synchronize(self.ctx.device)
-        arr = loc.detach().cpu().contiguous().numpy()
+            return self._gather_p2p(as_fp32, copy)
+        arr = self.local_owned().detach().cpu().contiguous().numpy()
         if not self.ctx.distributed:
             return arr.copy()
         parts = self.ctx.all_gather_object((self.block.start, arr))
@@ -834,7 +885,7 @@ class Solver:
             out[sl] = a
         return out
 
-    def _gather_p2p(self, as_fp32: bool) -> Optional[np.ndarray]:
+    def _gather_p2p(self, as_fp32: bool, copy: bool = True) -> Optional[np.ndarray]:
         from .ops import _lib
         from .parallel.arena import SharedBuffer
         cfg, G = self.cfg, self.ghost
@@ -848,6 +899,9 @@ class Solver:
                 self._gather_buf.close()
             self._gather_buf = SharedBuffer(self.ctx, cfg.cells * esz, owner=0)
             self._gather_key = key
+            self._gather_host = None
+            self._gather_ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True),
+                               torch.cuda.Event(enable_timing=True))
         shape3 = cfg.shape if self.ndim == 3 else (1,) + tuple(cfg.shape)
         if self.ndim == 3:
             z_lo, nz, y_lo, ny = G, self.own_shape[0], G, self.own_shape[1]
@@ -858,14 +912,55 @@ class Solver:
             plane_pitch = self.store_shape[0] * self.pitch
             dz0, dy0 = 0, self.block.start[0]
         self.ctx.barrier()          # rank 0's previous reader is done with the buffer
-        _lib.check(self._lib.mcp_pack_block(_MCP_DTYPE[cfg.dtype], 1 if cast else 0, self.bufs[self.cur].data_ptr(),
-                                            self.pitch, plane_pitch, z_lo, nz, y_lo, ny, cfg.width,
-                                            self._gather_buf.ptr, shape3[1], dz0, dy0, self._stream()), "mcp_pack_block")
+        ev0, ev1, ev2 = self._gather_ev
+        ev0.record()
+        if self.bits:
+            _lib.check(self._lib.mcp_pack_rows(3, 3, self.bufs[self.cur].data_ptr(), self.pitch, cfg.width, G,
+                                               G + self.own_shape[0], self._gather_buf.ptr, self.block.start[0],
+                                               self._stream()), "mcp_pack_rows")
+        else:
+            _lib.check(self._lib.mcp_pack_block(_MCP_DTYPE[cfg.dtype], 1 if cast else 0, self.bufs[self.cur].data_ptr(),
+                                                self.pitch, plane_pitch, z_lo, nz, y_lo, ny, cfg.width,
+                                                self._gather_buf.ptr, shape3[1], dz0, dy0, self._stream()),
+                       "mcp_pack_block")
+        ev1.record()
         torch.cuda.synchronize(self.ctx.device)
-        self.ctx.barrier()          # every rank's stores have landed in rank 0's memory
+        pack_ms = self.ctx.all_reduce_max(ev0.elapsed_time(ev1))     # also: every rank's stores have landed
+        own_bytes = int(np.prod(self.own_shape[:-1])) * cfg.width * esz
+        self.last_gather_stats = {"pack_ms": round(pack_ms, 4), "bytes_per_rank": own_bytes,
+                                  "bytes_into_rank0": cfg.cells * esz,
+                                  "rank0_ingress_gbs": round(cfg.cells * esz / (pack_ms * 1e-3) / 1e9, 2) if pack_ms > 0 else None,
+                                  "nvlink_peak_gbs": 770.0}
         if self.ctx.rank != 0:
             return None
-        return self._gather_buf.view(cfg.shape, out_t).cpu().numpy().astype(out_np, copy=False)
+        dev = self._gather_buf.view(cfg.shape, out_t)
+        if self._gather_host is None:
+            self._gather_host = torch.empty(cfg.shape, dtype=out_t).pin_memory()
+        self._gather_host.copy_(dev, non_blocking=True)
+        ev2.record()
+        ev2.synchronize()
+        self.last_gather_stats["d2h_ms"] = round(ev1.elapsed_time(ev2), 4)
+        arr = self._gather_host.numpy()
+        return arr.astype(out_np, copy=True) if copy else arr
+
+    def checksum(self) -> int:
+        """64-bit position-dependent checksum of the GLOBAL field (same value on every rank), computed on the devices:
+        per-rank sums over owned cells (``mcp_checksum2d``) added mod 2^64.  Equal checksums <=> equal fields (up to
+        hash collisions), for any rank count and backend -- the benchmark-size correctness check."""
+        if self.ndim != 2 or self.bits:
+            raise ValueError("checksum() covers 2-D fp32/fp64/int32 fields")
+        G = self.ghost
+        if self.ctx.is_cuda:
+            from .ops import _lib
+            out = torch.zeros(1, dtype=torch.int64, device=self.ctx.device)
+            _lib.check(self._lib.mcp_checksum2d(_MCP_DTYPE[self.cfg.dtype], self.bufs[self.cur].data_ptr(), self.pitch,
+                                                self.cfg.width, G, G + self.own_shape[0], self.block.start[0],
+                                                out.data_ptr(), self._stream()), "mcp_checksum2d")
+            local = int(out.cpu()[0]) & 0xFFFFFFFFFFFFFFFF
+        else:
+            local = oracle.checksum_rows(self.bufs[self.cur][G:G + self.own_shape[0], :self.cfg.width].numpy(),
+                                         self.block.start[0], self.cfg.width)
+        return sum(self.ctx.all_gather_object(local)) & 0xFFFFFFFFFFFFFFFF
 
     def gather_ascii(self) -> Optional[bytes]:
         """Life grids: the bytes the reference's ``print_array`` would print (kernel.cu:115-129), produced on the

@@ -47,7 +47,10 @@ def load(solver, directory: str) -> int:
     G = solver.ghost
     lo = [solver.block.start[a] - G for a in range(solver.ndim - 1)] + [0]
     hi = [solver.block.stop[a] + G for a in range(solver.ndim - 1)] + [solver.cfg.width]
-    loc = np.zeros(solver.store_shape, dtype=solver.npdtype)
+    # bit-packed life stores 32 cells per word: assemble CELLS (what save() wrote), pack them afterwards
+    bits = getattr(solver, "bits", False)
+    cells_shape = tuple(solver.store_shape[:-1]) + (solver.cfg.width,) if bits else tuple(solver.store_shape)
+    loc = np.zeros(cells_shape, dtype=solver.npdtype)
     for b in man["blocks"]:
         bs, bshape = b["start"], b["shape"]
         be = [s + n for s, n in zip(bs, bshape)]
@@ -60,6 +63,8 @@ def load(solver, directory: str) -> int:
         dst = tuple(slice(a - l, z - l) for a, z, l in zip(ov_lo, ov_hi, lo))
         loc[dst] = piece[src]
     import torch
+    if bits:
+        loc = solver._pack_bits(loc)
     t = torch.from_numpy(loc)
     for buf in solver.bufs:
         buf.copy_(t)

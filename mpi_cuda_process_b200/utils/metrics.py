@@ -28,12 +28,15 @@ def glups(cells: int, generations: int, ms: float) -> float:
 
 
 def roofline(cells_per_gpu: int, generations: int, ms: float, bytes_per_update: int, halo_bytes_per_gen: float = 0.0,
-             peaks: Optional[Dict] = None) -> Dict:
+             peaks: Optional[Dict] = None, time_block: int = 1) -> Dict:
     """Achieved fraction of the per-GPU roofline: the slower of HBM stencil time and NVLink halo time.
 
-    The HBM denominator is one read + one write per update per generation (``bytes_per_update``); a
-    temporally blocked kernel moves less than that, so its fraction can exceed 1 -- the actual DRAM bytes
-    are reported by ncu in profiles/.
+    ``fraction_of_roofline`` uses the one-pass denominator (one read + one write per update per generation); a
+    temporally blocked kernel advances ``time_block`` generations per pass over the field, so that fraction can
+    exceed 1.  ``fraction_of_time_block_roofline`` divides by the kernel's own bound instead: one read + one write
+    per ``time_block`` generations (what its DRAM traffic actually is, see the ncu summaries in profiles/); it is
+    the number to read as "how close to the memory system's limit" -- below 1 means something else (instruction
+    issue, FMA pipe) is the binding resource.
     """
     peaks = peaks or measured_peaks()
     hbm = peaks["hbm_gbs"] * 1e9
@@ -45,6 +48,10 @@ def roofline(cells_per_gpu: int, generations: int, ms: float, bytes_per_update: 
         "t_gen_us": t_gen * 1e6, "t_roofline_us": t_roof * 1e6,
         "bound": "hbm" if t_hbm >= t_halo else "nvlink",
         "fraction_of_roofline": t_roof / t_gen if t_gen > 0 else 0.0,
-        "effective_gbs": cells_per_gpu * bytes_per_update / t_gen / 1e9 if t_gen > 0 else 0.0,
+        "time_block": time_block,
+        "t_time_block_roofline_us": max(t_hbm / max(time_block, 1), t_halo / max(time_block, 1)) * 1e6,
+        "fraction_of_time_block_roofline": max(t_hbm, t_halo) / max(time_block, 1) / t_gen if t_gen > 0 else 0.0,
+        "one_pass_equivalent_gbs": cells_per_gpu * bytes_per_update / t_gen / 1e9 if t_gen > 0 else 0.0,
+        "dram_gbs_estimate": cells_per_gpu * bytes_per_update / max(time_block, 1) / t_gen / 1e9 if t_gen > 0 else 0.0,
         "peaks_source": peaks.get("source", "measured") + (" (of measured)" if peaks.get("source") == "measured" else " (of fallback)"),
     }

@@ -122,3 +122,19 @@ def test_run_to_tolerance_cpu():
         st = s.run_to_tolerance()
         assert st.residual_history[-1][1] <= 1e-2
         assert s.generation < 2000 and s.generation % 10 == 0
+
+
+def test_checksum_is_decomposition_independent():
+    from mpi_cuda_process_b200 import oracle as orc
+    f = orc.mdf_run(orc.mdf_init(23, 17), 6)
+    whole = orc.checksum_field(f)
+    parts = (orc.checksum_rows(f[:5], 0, 17) + orc.checksum_rows(f[5:16], 5, 17) + orc.checksum_rows(f[16:], 16, 17))
+    assert whole == parts & 0xFFFFFFFFFFFFFFFF
+    g = f.copy()
+    g[11, 3] = np.nextafter(g[11, 3], np.float32(1e9))
+    assert orc.checksum_field(g) != whole
+    cfg = RunConfig(workload="mdf", height=23, width=17, backend="cpu")
+    with Solver(cfg) as s:
+        s.initialize()
+        s.run(6)
+        assert s.checksum() == whole

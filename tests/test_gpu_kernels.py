@@ -198,59 +198,6 @@ def test_pack_rows_ascii_and_cast():
     assert torch.equal(d32, s64[:, :w].float())
 
 
-def test_two_ranks_emulated_on_one_gpu():
-    """Halo push addressing + flag counting of the fused kernel, two slabs on ONE GPU in one process.
-
-    Kernels that spin on each other must not run as separate launches on one GPU, so the two "ranks" are
-    advanced alternately one sweep at a time: every flag a launch waits for was raised by an earlier launch."""
-    lib_mod, lib = _lib()
-    h, w, tb, sweeps = 90, 200, 4, 5
-    G, pitch = tb, 224
-    rows = [45, 45]
-    starts = [0, 45]
-    ref0 = oracle.mdf_init(h, w)
-    ref0[1:-1, 1:-1] = np.random.default_rng(3).uniform(0, 100, (h - 2, w - 2)).astype(np.float32)
-    bufs, flags, plans = [], [], []
-    for r in range(2):
-        ra = rows[r] + 2 * G
-        loc = np.zeros((ra, pitch), dtype=np.float32)
-        lo, hi = starts[r] - G, starts[r] + rows[r] + G
-        cs, ce = max(lo, 0), min(hi, h)
-        loc[cs - lo:ce - lo, :w] = ref0[cs:ce]
-        t = torch.from_numpy(loc).cuda()
-        bufs.append([t.clone(), t.clone()])
-        flags.append(torch.zeros(8, dtype=torch.int64, device="cuda"))
-    for r in range(2):
-        d = lib_mod.FusedDesc()
-        d.op, d.dtype, d.h, d.w = 0, 0, h, w
-        d.row_start, d.rows_own, d.ghost, d.pitch = starts[r], rows[r], G, pitch
-        other = 1 - r
-        for i in range(2):
-            d.buf[i] = bufs[r][i].data_ptr()
-            d.up_buf[i] = bufs[other][i].data_ptr() if r == 1 else None
-            d.dn_buf[i] = bufs[other][i].data_ptr() if r == 0 else None
-        d.up_rows_own = rows[0] if r == 1 else 0
-        d.flags = flags[r].data_ptr()
-        d.up_flag = flags[0].data_ptr() + 8 if r == 1 else None
-        d.dn_flag = flags[1].data_ptr() if r == 0 else None
-        d.ylo, d.yhi, d.xlo, d.xhi = 1, h - 2, 1, w - 2
-        p = C.c_void_p()
-        lib_mod.check(lib.mcp_fused2d_create(C.byref(d), C.byref(p)))
-        plans.append(p)
-    for _ in range(sweeps):
-        for r in range(2):
-            lib_mod.check(lib.mcp_fused2d_run(plans[r], tb, tb, 0, None))
-            torch.cuda.synchronize()
-            lib_mod.check(lib.mcp_fused2d_status(plans[r]))
-    ref = oracle.mdf_run(ref0, tb * sweeps)
-    for r in range(2):
-        cur = lib.mcp_fused2d_parity(plans[r])
-        got = bufs[r][cur][G:G + rows[r], :w].cpu().numpy()
-        assert got.tobytes() == ref[starts[r]:starts[r] + rows[r]].tobytes(), f"rank {r}"
-        lib.mcp_fused2d_destroy(plans[r])
-    assert int(flags[0][1]) == sweeps * 2 and int(flags[1][0]) == sweeps * 2   # 2 strips per sweep
-
-
 def test_cli_on_gpu():
     import subprocess, sys
     r = subprocess.run([sys.executable, "-m", "mpi_cuda_process_b200", "--workload", "mdf", "--check", "--json"],
@@ -357,3 +304,60 @@ def test_life_bit_packed_device_init_matches_hash_oracle():
         assert (s.gather() == oracle.life_init_hash(77, 391, 0.15, 5)).all()
         s.run(6)
         assert (s.gather() == oracle.life_run(oracle.life_init_hash(77, 391, 0.15, 5), 6)).all()
+
+
+def test_checkpoint_roundtrip_bit_packed_life(tmp_path):
+    """save() writes unpacked cells, load() must pack them again (w > pitch_words used to raise, small w
+    silently stored cells as words)."""
+    from mpi_cuda_process_b200.utils import checkpoint as ckpt
+    for h, w in ((40, 70), (33, 1100)):
+        cfg = RunConfig(workload="life", dtype="bits", height=h, width=w, backend="fused", time_block=2)
+        d = tmp_path / f"c{w}"
+        with Solver(cfg) as s:
+            s.initialize()
+            s.run(4)
+            ckpt.save(s, str(d))
+        with Solver(cfg) as s:
+            assert ckpt.load(s, str(d)) == 4
+            s.run(6)
+            got = s.gather()
+        ref = oracle.life_run(oracle.life_init_reference(h, w), 10)
+        assert (got == ref).all()
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "fp64"])
+def test_device_checksum_matches_numpy_restatement(dtype):
+    cfg = RunConfig(workload="mdf", height=150, width=333, backend="fused", time_block=4, dtype=dtype, init="hash", seed=3)
+    with Solver(cfg) as s:
+        s.initialize()
+        s.run(12)
+        got = s.checksum()
+        field = s.gather()
+    assert got == oracle.checksum_field(field)
+    assert field.tobytes() == oracle.run_field(cfg, oracle.init_field(cfg), 12).tobytes()
+
+
+def test_gather_bits_unpacks_on_the_device():
+    cfg = RunConfig(workload="life", dtype="bits", height=70, width=1000, backend="fused", time_block=2)
+    with Solver(cfg) as s:
+        s.initialize()
+        s.run(5)
+        got = s.gather()
+        assert s.last_gather_stats["bytes_into_rank0"] == 70 * 1000 * 4
+    assert (got == oracle.life_run(oracle.life_init_reference(70, 1000), 5)).all()
+
+
+def test_final_residual_single_launch_matches_history():
+    """residual="final": one launch, residual-free row loop for all but the last time block, same value as the
+    per-block history's last entry and as the oracle."""
+    cfg = RunConfig(workload="mdf", height=200, width=300, backend="fused", time_block=4, residual="linf")
+    with Solver(cfg) as s:
+        s.initialize()
+        st = s.run(40, residual="final")
+        assert st.launches == 1 and len(st.residual_history) == 1
+        final = st.residual_history[-1][1]
+    with Solver(cfg) as s:
+        s.initialize()
+        hist = s.run(40, residual=True).residual_history
+    u = oracle.mdf_run(oracle.mdf_init(200, 300), 39)
+    assert final == hist[-1][1] == oracle.residual(oracle.mdf_step(u), u, "linf")

@@ -12,8 +12,8 @@ def test_roofline_arithmetic():
     # 64 Mi cells, 8 B/update, 10 generations in 1 ms -> 5.4 TB/s effective
     r = metrics.roofline(1 << 26, 10, 1.0, 8, 0.0, peaks)
     assert r["bound"] == "hbm"
-    assert abs(r["effective_gbs"] - (1 << 26) * 8 * 10 / 1e-3 / 1e9) < 1e-6
-    assert abs(r["fraction_of_roofline"] - r["effective_gbs"] / 6400.0) < 1e-9
+    assert abs(r["one_pass_equivalent_gbs"] - (1 << 26) * 8 * 10 / 1e-3 / 1e9) < 1e-6
+    assert abs(r["fraction_of_roofline"] - r["one_pass_equivalent_gbs"] / 6400.0) < 1e-9
     assert "of measured" in r["peaks_source"]
     # a tiny grid with a huge halo is NVLink-bound
     r2 = metrics.roofline(1024, 1, 1.0, 8, 1e9, peaks)
