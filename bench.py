@@ -52,6 +52,7 @@ def parse_args(argv=None):
                    help="weak: --height is per GPU (BASELINE.json config 4 uses 8192 x 8192 per GPU)")
     p.add_argument("--chunk-rows", type=int, default=0, help="rows per tile of the schedule (0 = default)")
     p.add_argument("--sync-mode", type=int, default=None, help="1 = grid barrier between sweeps, 2 = dataflow flags")
+    p.add_argument("--prefetch", type=int, default=None, help="0 = no next-tile TMA prefetch (A/B)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--halo-message", default="row", choices=["row", "element"])
     p.add_argument("--coarse-halo-flags", action="store_true", help="one arrival counter per neighbour instead of per-strip flags")
@@ -108,7 +109,7 @@ def main(argv=None) -> int:
                     backend=backend,
                     decomposition=args.decomposition, seed=0 if args.workload == "life" else None,
                     time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
-                    extra={"chunk_rows": args.chunk_rows, "sync_mode": args.sync_mode,
+                    extra={"chunk_rows": args.chunk_rows, "sync_mode": args.sync_mode, "prefetch": args.prefetch,
                            "coarse_halo_flags": args.coarse_halo_flags})
     K, W = args.steps, max(args.warmup, 0)
 
@@ -156,36 +157,60 @@ def main(argv=None) -> int:
             tb = s.time_block
             d2h = 32                                       # result block: status, sweeps done, (sum of squares, max)
 
+            # Every step: H2D of the step's input slab from pinned memory, one solve (one launch), D2H of the step's
+            # result (status + global residual).  The host reads step i's result AFTER it has enqueued step i+1, so the
+            # ranks' launches are not separated by a host round trip per step (the copy itself happens every step).
+            pending = []
+
             def one_step():
                 s.commit_input()                          # this step's input (uploaded while the previous step ran)
                 s.stage_input(host)                       # pinned host -> device for the next step, overlapped
-                st = s.run(gps, residual="final", timed=False)   # fused residual of the last generation, read back
-                return st.residual_history[-1][1] if st.residual_history else s.residual()
+                pending.append(s.run_async(gps))          # solve + async 32-byte result copy
+                return pending.pop(0).wait() if len(pending) > 1 else None
+
+            def drain():
+                r = None
+                while pending:
+                    r = pending.pop(0).wait()
+                return r
 
             s.stage_input(host)
             for _ in range(min(W, 2)):
                 one_step()
+            drain()
             torch.cuda.synchronize()
             ctx.barrier()
             t0 = time.perf_counter()
             last = None
             l0 = s.total_stats.launches
             for _ in range(K):
-                last = one_step()
+                r = one_step()
+                last = r if r is not None else last
+            last = drain()                                # the last step's result
             torch.cuda.synchronize()                      # includes the upload issued in the last step
             t1 = time.perf_counter()
             e2e_ms = ctx.all_reduce_max((t1 - t0) * 1e3)
+            # what bounds a step: the solve, or the host -> device upload of its input?  (device-timed, max over ranks;
+            # "overlapped" = while the solve of the previous step runs, "alone" = all ranks uploading, GPUs idle)
+            h2d_overlapped_ms = ctx.all_reduce_max(s.last_upload_ms() or 0.0)
+            ctx.barrier()
+            s.stage_input(host)
+            h2d_alone_ms = ctx.all_reduce_max(s.last_upload_ms() or 0.0)
             e2e = {"value": round(cells * gps * K / (e2e_ms * 1e-3) / 1e9, 3), "unit": "GLUPS",
                    "ms_per_step": round(e2e_ms / K, 4), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "result": "kernel status + global max|u'-u| of the last iteration (32-byte result block)",
                    "last_residual": last, "overlap": "H2D of step i+1 overlaps compute of step i (side stream)",
-                   "launches_per_step": (s.total_stats.launches - l0) / max(K, 1)}
+                   "launches_per_step": (s.total_stats.launches - l0) / max(K, 1),
+                   "h2d_ms_overlapped_max": round(h2d_overlapped_ms, 3), "h2d_ms_alone_max": round(h2d_alone_ms, 3),
+                   "h2d_gbs_per_gpu_overlapped": round(h2d / (h2d_overlapped_ms * 1e-3) / 1e9, 2) if h2d_overlapped_ms > 0 else None,
+                   "bound": "upload" if h2d_overlapped_ms > 0.9 * e2e_ms / K else "solve"}
 
             # ---- the same, with the solution field gathered to rank 0 and copied to the host every step ----
             Kg = max(1, min(K, 4))
 
             def one_step_gather():
-                r = one_step()
+                one_step()
+                r = drain()                               # the field is wanted now: wait for this step
                 f = s.gather(copy=False)                  # fused gather+pack over NVLink, D2H into pinned memory
                 return r, (None if f is None else float(f[0, 0]))
 

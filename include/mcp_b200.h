@@ -44,6 +44,7 @@ extern "C" {
 #define MCP_OPT_DEBUG_FLAGS 2 /* bit 2 (4): per-tile timing trace; bit 3 (8): pseudo-random delays in front of halo
                                * pushes and publishes (protocol stress tests) */
 #define MCP_OPT_SYNC_MODE 3   /* 0 = choose, 1 = device-side grid barrier between sweeps, 2 = per-chunk dataflow flags */
+#define MCP_OPT_PREFETCH 4    /* dataflow: 1 (default) = a tile's tail puts the next tile's first TMA stages in flight */
 
 /* mcp_fused2d_stop_reason: why the last run-to-tolerance ended */
 #define MCP_STOP_NONE 0
@@ -186,10 +187,13 @@ int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost,
 /* Same with the schedule kind: mode 0 = grid-barrier schedule, 1 = barrier-free (dataflow) schedule. */
 int mcp_fused2d_plan_schedule2(int op, int dtype, int w, int rows_own, int ghost, int time_block, int grid,
                                int chunk_rows, int mode, int* rows_out, int max_entries, int* n_strips);
-/* Tile trace (mcp_fused2d_set_option(plan, MCP_OPT_DEBUG_FLAGS, 4) before the run): duration in ns of every tile of the last sweep, in
- * queue order, with its chunk and strip index.  Returns the number of entries. */
+/* Tile trace (mcp_fused2d_set_option(plan, MCP_OPT_DEBUG_FLAGS, 4) before the run): ns that every tile spent in its
+ * row loop, summed over the sweeps of the last launch, in queue order, with its chunk and strip index.  Returns the
+ * number of entries.  mcp_fused2d_tile_trace2 selects the quantity: 0 = row loop, 1 = waiting for dependencies
+ * (previous-sweep tiles, neighbour GPUs' halo flags), 2 = halo push + publish. */
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* plan, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
                            int max_entries);
+int mcp_fused2d_tile_trace2(mcp_fused2d_plan* plan, int time_block, int which, uint32_t* ns_out, int max_entries);
 /* Protocol check: the number of halo arrivals this rank should have received so far from rank-1 and rank+1.
  * After a synchronised run the local counters flags[0], flags[1] must equal these (when that neighbour exists). */
 int mcp_fused2d_expected_flags(const mcp_fused2d_plan* plan, uint64_t* up_dn);

@@ -100,6 +100,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused2d_tile_at.argtypes = [i, i, i, C.POINTER(i), C.POINTER(i)]
     lib.mcp_fused2d_plan_schedule.argtypes = [i, i, i, i, i, i, i, i, vp, i, C.POINTER(i)]
     lib.mcp_fused2d_tile_trace.argtypes = [vp, i, vp, vp, vp, i]
+    lib.mcp_fused2d_tile_trace2.argtypes = [vp, i, i, vp, i]
     lib.mcp_fused2d_expected_flags.argtypes = [vp, vp]
     lib.mcp_fused2d_parity.argtypes = [vp]
     lib.mcp_fused2d_set_parity.argtypes = [vp, i]

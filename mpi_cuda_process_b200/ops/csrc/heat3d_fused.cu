@@ -272,10 +272,12 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             __syncthreads();
             if (tid == 0) {
                 const bool touch[4] = {f_zm, f_zp, f_ym, f_yp};
+                bool fenced = false;  // one system-scope fence (a round trip to the peers), then relaxed signals
                 for (int f = 0; f < 4; ++f)
                     if (touch[f] && p.nbr_buf[f][0] != nullptr) {
-                        ptx::fence_acq_rel_sys();
-                        ptx::red_add_release_sys(p.nbr_flag[f], 1ull);
+                        if (!fenced) ptx::fence_acq_rel_sys();
+                        fenced = true;
+                        ptx::red_add_relaxed_sys(p.nbr_flag[f], 1ull);
                     }
             }
         }

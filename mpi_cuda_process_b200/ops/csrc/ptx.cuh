@@ -108,6 +108,15 @@ __device__ __forceinline__ void red_add_release_sys(unsigned long long* p, unsig
 __device__ __forceinline__ void red_add_release_gpu(unsigned long long* p, unsigned long long v) {
     asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// Relaxed (but strong, system-scope) signal writes: placed AFTER one fence.acq_rel.sys they form a release pattern, so
+// several flags can be raised behind a single fence -- every .release store or red would pay its own fence, i.e. its
+// own round trip to the peer GPU when NVLink stores are outstanding.
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_relaxed_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 

@@ -93,7 +93,9 @@ struct Fused2dParams {
     unsigned long long* grid_bar;
     unsigned long long* tile_ctr;
     unsigned* tile_done;  // [n_tiles] last sweep (1-based, within this launch) each tile has completed
-    unsigned* tile_ns;    // [n_tiles] trace (debug_flags & 4): duration of the tile in the last sweep it ran, in ns
+    unsigned* tile_ns;    // trace (debug_flags & 4), ns summed over the launch's sweeps: [0][q] row loop,
+                          // [1][q] waiting for dependencies, [2][q] halo push + publish; planes of trace_cap words
+    int trace_cap;
     int* status;
     double* partials;  // [2][n_tiles][2]
     double* res_out;   // [kMaxResSlots][2]
@@ -126,6 +128,7 @@ struct Fused2dParams {
     int sweeps, first_parity, res_slot0;
     int res_first_sweep;  // sweeps >= this accumulate the residual (0 = every sweep, sweeps - 1 = the last one only)
     int debug_flags;
+    int prefetch;   // barrier-free path: put the next tile's first TMA stages in flight from the current tile's tail
     int sync_mode;  // 1 = grid barrier between sweeps, 2 = per-tile dataflow flags (no barrier)
 };
 
@@ -133,7 +136,7 @@ struct Fused2dParams {
 
 
 // Schedule arithmetic shared by the host plan and the kernel (no tables: a tile start costs no dependent loads).
-// n_chunks - 1 chunks of chunk_r rows and a last one that takes the remainder (chunk_r <= its height < 2 chunk_r).
+// n_chunks - 1 chunks of chunk_r rows and a last one that takes the remainder (between half and 1.5 x chunk_r).
 __host__ __device__ __forceinline__ int chunk_row_of(int own_lo, int rows, int n_chunks, int chunk_r, int c) {
     return c < n_chunks ? own_lo + c * chunk_r : own_lo + rows;
 }
@@ -342,12 +345,23 @@ __device__ __forceinline__ void wait_ghost(const Fused2dParams& p, const int dir
     }
 }
 
+// The tile this warp will run next (barrier-free path).  While the current tile consumes its last kStages stages, the
+// ring slots they free are refilled with the FIRST stages of the next tile -- if a non-blocking look at its nine
+// dependency flags finds them all set.  The next tile then starts with its data in flight (no TMA refill bubble), and
+// the publish fence of the current tile overlaps that flight.  Nothing here ever blocks, so the ticket-order argument
+// for freedom from deadlock is untouched; a failed probe just falls back to the ordinary start of a tile.
+struct NextTile {
+    const CUtensorMap* tm_in;
+    int valid;   // 0 = no prefetch (last ticket, ghost-row dependencies, grid-barrier path)
+    int sw, chunk, strip, x_ld, ys, n_it;
+};
+
 template <class Op, int TB, bool RES>
 __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUtensorMap* tm_in,
                                              typename Op::T* __restrict__ out, typename Op::T* up_out,
                                              typename Op::T* dn_out, const int x_ld, const int y0, const int y1,
                                              uint8_t* my_smem, uint64_t* bars, uint32_t& it, const int lane,
-                                             double& rs, double& rm) {
+                                             double& rs, double& rm, const NextTile& nx, int& pre) {
     using T = typename Op::T;
     using V = typename Op::V;
     using Row = typename Op::Row;
@@ -379,8 +393,18 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
 
     if (lane == 0) {
         const int npro = n_it < kStages ? n_it : kStages;
-        for (int i = 0; i < npro; ++i) issue(it + i, ys + i * kRowsPerStage);
+        for (int i = pre; i < npro; ++i) issue(it + i, ys + i * kRowsPerStage);  // `pre` stages are in flight already
     }
+    pre = 0;
+    // probe of the next tile's dependency flags: loads issued one stage before their values are looked at
+    unsigned probe = 0xffffffffu;
+    const int i_probe = n_it - kStages - 1;
+    const unsigned* probe_ptr = nullptr;
+    if (nx.valid && nx.sw > 0 && lane < 9) {
+        const int c2 = nx.chunk + lane / 3 - 1, s2 = nx.strip + lane % 3 - 1;
+        if (c2 >= 0 && c2 < p.n_chunks && s2 >= 0 && s2 < p.n_strips) probe_ptr = &p.tile_done[c2 * p.n_strips + s2];
+    }
+    bool next_ok = false;
 
     // output pointer of the row produced by input-row counter c: local row ys + c - TB
     T* optr = out + (long long)(ys - TB) * p.pitch + cx;
@@ -403,7 +427,29 @@ __device__ __forceinline__ void process_tile(const Fused2dParams& p, const CUten
             stage_rows<Op, TB, 0, RES>(L, sp, optr, p.pitch, cbase, n_in, gy_base, p.ylo, p.yhi, colfix, lane_valid,
                                        lane_store, rs, rm);
         __syncwarp();
-        if (lane == 0 && i + kStages < n_it) issue(it + kStages, ys + (i + kStages) * kRowsPerStage);
+        if (i + kStages < n_it) {
+            if (lane == 0) issue(it + kStages, ys + (i + kStages) * kRowsPerStage);
+            if (i == i_probe && probe_ptr != nullptr)
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(probe) : "l"(probe_ptr) : "memory");
+        } else if (nx.valid) {
+            const int k = i + kStages - n_it;  // stage of the NEXT tile that fits the slot just freed
+            if (k == 0) {
+                if (i_probe < 0 && probe_ptr != nullptr)  // tile too short for the early probe
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(probe) : "l"(probe_ptr) : "memory");
+                next_ok = __all_sync(0xffffffffu, probe >= (unsigned)nx.sw);
+                if (next_ok && lane == 0) ptx::fence_proxy_async();
+                __syncwarp();
+            }
+            if (next_ok && k < nx.n_it) {
+                if (lane == 0) {
+                    const uint32_t st2 = (it + kStages) % kStages;
+                    ptx::mbar_arrive_expect_tx(&bars[st2], kStageBytes);
+                    ptx::tma_load_2d(my_smem + st2 * kStageBytes, nx.tm_in, &bars[st2], nx.x_ld,
+                                     nx.ys + k * kRowsPerStage);
+                }
+                pre = k + 1;
+            }
+        }
         ++it;
     }
 
@@ -469,8 +515,8 @@ __device__ __noinline__ void reduce_and_exchange(const Fused2dParams& p, const d
                 p.peer_inbox[r][off] = sa;
                 p.peer_inbox[r][off + 1] = sb;
             }
-            ptx::fence_acq_rel_sys();
-            for (int r = 0; r < p.world; ++r) ptx::red_add_release_sys(p.peer_res_flag[r], 1ull);
+            ptx::fence_acq_rel_sys();  // one fence, then relaxed signals (a release pattern for every peer)
+            for (int r = 0; r < p.world; ++r) ptx::red_add_relaxed_sys(p.peer_res_flag[r], 1ull);
             if (wait_counter_sys(p, p.res_flag, (seq + 1ull) * (unsigned long long)p.world)) {
                 const volatile double* in = p.peer_inbox[p.rank] + (size_t)(seq % kResRing) * kMaxRanks * 2;
                 sa = 0.0;
@@ -547,7 +593,8 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
 
     const bool dataflow = p.sync_mode == 2;
     // One tile of one sweep.  RES_NOW: this sweep accumulates the residual (a compile-time copy of the row loop).
-    auto run_tile = [&](const int sw, const int q, double* partials, auto res_now) {
+    int pre = 0;  // stages of the tile about to start that the previous tile has already put in flight
+    auto run_tile = [&](const int sw, const int q, double* partials, auto res_now, const NextTile& nx) {
         constexpr bool RES_NOW = decltype(res_now)::value;
         const int par = (p.first_parity + sw) & 1;
         const CUtensorMap* tm_in = par ? tmB : tmA;
@@ -561,7 +608,11 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
         T* up_out = top ? reinterpret_cast<T*>(p.up_buf[par ^ 1]) : nullptr;
         T* dn_out = bot ? reinterpret_cast<T*>(p.dn_buf[par ^ 1]) : nullptr;
 
-        if (dataflow && sw > 0 && lane < 9) {
+        const bool trace = (p.debug_flags & 4) != 0;
+        const unsigned long long t_enter = trace ? ptx::globaltimer_ns() : 0ull;
+        if (pre > 0) {
+            // dependencies were found settled (and fenced) when the previous tile put our first stages in flight
+        } else if (dataflow && sw > 0 && lane < 9) {
             // Dataflow instead of a grid barrier: this tile reads what its (up to) 9 neighbours wrote in the
             // previous sweep and overwrites what they read then -- both are settled once they have finished it.
             // One lane per neighbour, so the nine acquire loads are in flight together.
@@ -569,19 +620,21 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
             if (c2 >= 0 && c2 < p.n_chunks && s2 >= 0 && s2 < p.n_strips)
                 wait_tile_done(p, &p.tile_done[c2 * p.n_strips + s2], (unsigned)sw);
         }
-        if (up_out != nullptr) wait_ghost(p, 0, sw, strip, lane);
-        if (dn_out != nullptr) wait_ghost(p, 1, sw, strip, lane);
-        __syncwarp();
-        if (lane == 0) ptx::fence_proxy_async();  // generic-proxy stores (other SMs, peers) -> our TMA loads
-        __syncwarp();
-        if (aborted(p)) return;
+        if (pre == 0) {
+            if (up_out != nullptr) wait_ghost(p, 0, sw, strip, lane);
+            if (dn_out != nullptr) wait_ghost(p, 1, sw, strip, lane);
+            __syncwarp();
+            if (lane == 0) ptx::fence_proxy_async();  // generic-proxy stores (other SMs, peers) -> our TMA loads
+            __syncwarp();
+            if (aborted(p)) return;
+        }
 
         double rs = 0.0, rm = 0.0;
-        const bool trace = (p.debug_flags & 4) != 0;
         const unsigned long long t_begin = trace ? ptx::globaltimer_ns() : 0ull;
         if ((p.debug_flags & 8) && (top || bot)) injected_delay(p, (unsigned)(sw * 131071 + strip * 2 + 0));
-        process_tile<Op, TB, RES_NOW>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm);
-        if (trace && lane == 0) p.tile_ns[q] = (unsigned)(ptx::globaltimer_ns() - t_begin);
+        process_tile<Op, TB, RES_NOW>(p, tm_in, out, up_out, dn_out, x_ld, y0, y1, my_smem, bars, it, lane, rs, rm, nx,
+                                      pre);
+        const unsigned long long t_end = trace ? ptx::globaltimer_ns() : 0ull;
 
         if (RES_NOW) {
 #pragma unroll
@@ -598,22 +651,35 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
         __syncwarp();
         if ((p.debug_flags & 8) && (top || bot)) injected_delay(p, (unsigned)(sw * 131071 + strip * 2 + 1));
         if (lane == 0) {
-            if (dataflow) {
-                ptx::fence_proxy_async();
+            const bool cut = up_out != nullptr || dn_out != nullptr;
+            if (dataflow) ptx::fence_proxy_async();
+            if (cut) {
+                // ONE system-scope fence covers the local rows, the rows pushed to both neighbours and every flag
+                // below: with NVLink stores outstanding each fence is a round trip to the peer (measured ~3.5 us;
+                // four of them per boundary tile made its publish 29 us, profiles/r2/)
+                ptx::fence_acq_rel_sys();
+                if (dataflow)
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(&p.tile_done[chunk * p.n_strips + strip]),
+                                 "r"((unsigned)(sw + 1))
+                                 : "memory");
+                const unsigned long long done_seq = p.seq_base + (unsigned long long)sw + 1ull;
+                if (up_out != nullptr) {
+                    if (p.up_strip_flag != nullptr) ptx::st_relaxed_sys(&p.up_strip_flag[strip], done_seq);
+                    ptx::red_add_relaxed_sys(p.up_flag, 1ull);
+                }
+                if (dn_out != nullptr) {
+                    if (p.dn_strip_flag != nullptr) ptx::st_relaxed_sys(&p.dn_strip_flag[strip], done_seq);
+                    ptx::red_add_relaxed_sys(p.dn_flag, 1ull);
+                }
+            } else if (dataflow) {
                 asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&p.tile_done[chunk * p.n_strips + strip]),
                              "r"((unsigned)(sw + 1))
                              : "memory");
             }
-            const unsigned long long done_seq = p.seq_base + (unsigned long long)sw + 1ull;
-            if (up_out != nullptr) {
-                ptx::fence_acq_rel_sys();
-                if (p.up_strip_flag != nullptr) ptx::st_release_sys(&p.up_strip_flag[strip], done_seq);
-                ptx::red_add_release_sys(p.up_flag, 1ull);
-            }
-            if (dn_out != nullptr) {
-                ptx::fence_acq_rel_sys();
-                if (p.dn_strip_flag != nullptr) ptx::st_release_sys(&p.dn_strip_flag[strip], done_seq);
-                ptx::red_add_release_sys(p.dn_flag, 1ull);
+            if (trace) {
+                p.tile_ns[q] += (unsigned)(t_end - t_begin);
+                p.tile_ns[p.trace_cap + q] += (unsigned)(t_begin - t_enter);
+                p.tile_ns[2 * p.trace_cap + q] += (unsigned)(ptx::globaltimer_ns() - t_end);
             }
         }
     };
@@ -634,12 +700,30 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
             if (!aborted(p)) {
                 const int sw = (int)(t / (unsigned long long)n_tiles);
                 const int q = (int)(t - (unsigned long long)sw * n_tiles);
+                NextTile nx;
+                nx.valid = 0;
+                if (t_next < total && p.prefetch) {
+                    nx.sw = (int)(t_next / (unsigned long long)n_tiles);
+                    decode_tile((int)(t_next - (unsigned long long)nx.sw * n_tiles), p.n_strips, p.n_chunks, nx.chunk,
+                                nx.strip);
+                    // tiles that read ghost rows wait for NVLink flags at their own start: no prefetch for those
+                    const bool ghost = (nx.chunk == 0 && p.up_buf[0] != nullptr) ||
+                                       (nx.chunk == p.n_chunks - 1 && p.dn_buf[0] != nullptr);
+                    if (!ghost) {
+                        const int ny0 = chunk_row(p, nx.chunk), ny1 = chunk_row(p, nx.chunk + 1);
+                        nx.valid = 1;
+                        nx.tm_in = ((p.first_parity + nx.sw) & 1) ? tmB : tmA;
+                        nx.x_ld = nx.strip * OUTW - M * VEC;
+                        nx.ys = ny0 - TB;
+                        nx.n_it = (ny1 - ny0 + 2 * TB + kRowsPerStage - 1) / kRowsPerStage;
+                    }
+                }
                 bool res_now = false;
                 if constexpr (RES) res_now = sw >= p.res_first_sweep;
                 if constexpr (RES) if (res_now) {
                     // only the LAST sweep may carry the residual on this path (host-enforced): the last tile to
                     // finish it reduces the partials and runs the cross-rank exchange
-                    run_tile(sw, q, p.partials, std::true_type{});
+                    run_tile(sw, q, p.partials, std::true_type{}, nx);
                     unsigned last = 0;
                     __syncwarp();
                     if (lane == 0) {
@@ -656,7 +740,7 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
                         }
                     }
                 }
-                if (!res_now) run_tile(sw, q, nullptr, std::false_type{});
+                if (!res_now) run_tile(sw, q, nullptr, std::false_type{}, nx);
             }
             t = t_next;
         }
@@ -668,6 +752,8 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
     // history and run-to-tolerance, where the stop decision of sweep k must reach every CTA before sweep k+2)
     unsigned long long epoch = 0;
     int executed = 0;
+    NextTile no_next;
+    no_next.valid = 0;
     for (int sw = 0; sw < p.sweeps; ++sw) {
         const bool res_now = RES && sw >= p.res_first_sweep;
         if (RES && p.stop_mode != 0 && sw > 0) {
@@ -692,11 +778,11 @@ __device__ __forceinline__ void fused2d_body(const CUtensorMap* tmA, const CUten
             if (!aborted(p)) {
                 if constexpr (RES) {
                     if (res_now)
-                        run_tile(sw, q, partials, std::true_type{});
+                        run_tile(sw, q, partials, std::true_type{}, no_next);
                     else
-                        run_tile(sw, q, partials, std::false_type{});
+                        run_tile(sw, q, partials, std::false_type{}, no_next);
                 } else {
-                    run_tile(sw, q, partials, std::false_type{});
+                    run_tile(sw, q, partials, std::false_type{}, no_next);
                 }
             }
             q = q_next;
@@ -788,6 +874,7 @@ struct mcp_fused2d_plan {
     unsigned long long timeout_ns;
     int debug_flags;
     int sync_mode;  // 0 = choose per launch, 1 = barrier, 2 = dataflow
+    int prefetch;
 };
 
 namespace {
@@ -816,7 +903,8 @@ int max_tb(int op, int dtype) {
 
 int tb_index(int tb) { return tb == 1 ? 0 : tb == 2 ? 1 : tb == 4 ? 2 : 3; }
 
-// Chunks of `r` rows (the last one takes the remainder, so r <= its height < 2r); every chunk holds >= G rows.
+// Chunks of `r` rows; the last one takes the remainder when that is at least max(G, r/2) rows, else the remainder is
+// folded into the chunk before it (so the last chunk is never a long straggler); every chunk holds >= G rows.
 // r + 2*TB is made a whole number of TMA stages, so a tile neither loads nor pushes rows it does not need.
 void fill_geometry(int rows, int own_lo, int G, int tb, int r, Geometry* g) {
     r = std::max(std::max(r, G), 1);
@@ -824,7 +912,8 @@ void fill_geometry(int rows, int own_lo, int G, int tb, int r, Geometry* g) {
         r -= (r + 2 * tb) % kRowsPerStage;
         while (r < G) r += kRowsPerStage;
     }
-    int nc = std::max(1, rows / r);
+    int nc = std::max(1, (rows + r - 1) / r);
+    if (nc > 1 && rows - (nc - 1) * r < std::max(G, r / 2)) nc -= 1;
     if (nc > kMaxChunks) {
         nc = kMaxChunks;
         r = rows / nc;
@@ -862,7 +951,15 @@ void build_dataflow_geometry(const mcp_fused2d_desc& d, int grid, int tb, Geomet
     int r = d.chunk_rows;
     // measured on B200 (profiles/): never below 16 time blocks -- a tile pays ~2 us of TMA refill and a publish on top
     // of the pre-roll, which short tiles cannot amortise
-    if (r <= 0) r = std::max(16 * tb, std::min(64 * tb, formula_rows(d, grid, tb, ns)));
+    if (r <= 0) {
+        r = std::max(16 * tb, std::min(64 * tb, formula_rows(d, grid, tb, ns)));
+        // at least two tiles per warp and sweep: a warp that draws a tile of the NEXT sweep then finds the tiles it
+        // depends on (drawn a tile-time earlier) finished instead of idling for them (measured cliff: 1.6 tiles per
+        // warp run at 0.65 of the rate of 2.0, profiles/)
+        const int NW = grid * warps_for(op_kind(d), tb);
+        const int cap = (int)((long long)rows * ns / (2LL * NW));
+        r = std::max(std::max(G, 4 * tb), std::min(r, cap));
+    }
     fill_geometry(rows, d.ghost, G, tb, r, g);
 }
 
@@ -950,6 +1047,7 @@ int fill_params(mcp_fused2d_plan* pl, const LaunchSpec& ls, Fused2dParams* out) 
     p.ctr_base = pl->ctr_base;
     p.tile_done = pl->tile_done;
     p.tile_ns = pl->tile_ns;
+    p.trace_cap = (int)pl->partials_cap_tiles;
     pl->last_tiles = ns * g.n_chunks();
     p.result = pl->result;
     p.status = &pl->result->status;
@@ -997,6 +1095,7 @@ int fill_params(mcp_fused2d_plan* pl, const LaunchSpec& ls, Fused2dParams* out) 
     p.stop_mode = ls.stop_mode;
     p.stop_thresh = ls.stop_thresh;
     p.sync_mode = ls.mode == 0 ? 1 : 2;
+    p.prefetch = pl->prefetch;
     return MCP_OK;
 }
 
@@ -1079,6 +1178,7 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     pl->timeout_ns = 20ull * 1000000000ull;
     pl->debug_flags = 0;
     pl->sync_mode = 0;
+    pl->prefetch = 1;
     pl->grid_bar = nullptr;
     pl->result = nullptr;
     pl->partials = nullptr;
@@ -1118,8 +1218,8 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
         (e = cudaMalloc(&pl->partials, pl->partials_cap_tiles * 4 * sizeof(double))) != cudaSuccess ||
         (e = cudaMalloc(&pl->res_out, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
         (e = cudaMemset(pl->res_out, 0, kMaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
-        (e = cudaMalloc(&pl->tile_ns, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
-        (e = cudaMemset(pl->tile_ns, 0, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
+        (e = cudaMalloc(&pl->tile_ns, 3 * pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
+        (e = cudaMemset(pl->tile_ns, 0, 3 * pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess ||
         (e = cudaMalloc(&pl->tile_done, pl->partials_cap_tiles * sizeof(unsigned))) != cudaSuccess) {
         set_error("mcp_fused2d_create: scratch allocation failed: %s", cudaGetErrorString(e));
         mcp_fused2d_destroy(pl);
@@ -1144,6 +1244,9 @@ int mcp_fused2d_set_option(mcp_fused2d_plan* pl, int option, long long value) {
         case MCP_OPT_SYNC_MODE:
             MCP_REQUIRE(value >= 0 && value <= 2, "sync mode must be 0 (choose), 1 (grid barrier) or 2 (dataflow)");
             pl->sync_mode = (int)value;
+            return MCP_OK;
+        case MCP_OPT_PREFETCH:
+            pl->prefetch = value != 0;
             return MCP_OK;
         default: break;
     }
@@ -1182,6 +1285,8 @@ static int launch(mcp_fused2d_plan* pl, const LaunchSpec& ls, cudaStream_t strea
     if (ls.stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(&pl->result->stop_word, 0, 2 * sizeof(int), stream));
     if (ls.mode == 1)
         MCP_CUDA_TRY(cudaMemsetAsync(pl->tile_done, 0, (size_t)p.n_strips * p.n_chunks * sizeof(unsigned), stream));
+    if (pl->debug_flags & 4)
+        MCP_CUDA_TRY(cudaMemsetAsync(pl->tile_ns, 0, 3 * pl->partials_cap_tiles * sizeof(unsigned), stream));
     const int smem = smem_bytes_for(warps);
     void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
     MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -1375,8 +1480,19 @@ int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost,
                                       max_entries, n_strips);
 }
 
-// Trace (MCP_OPT_DEBUG_FLAGS & 4): duration in ns of every tile in the last sweep it ran, in queue order, with its
-// (group, strip) so that a host tool can see which tiles are the critical path.
+// Trace (MCP_OPT_DEBUG_FLAGS & 4): per tile, in queue order, the ns spent over all sweeps of the last launch in
+// the row loop (which = 0), waiting for dependencies (1) and in halo push + publish (2), with its (chunk, strip), so
+// that a host tool can see which tiles are the critical path and where ranks wait for each other.
+int mcp_fused2d_tile_trace2(mcp_fused2d_plan* pl, int time_block, int which, uint32_t* ns_out, int max_entries) {
+    MCP_REQUIRE(pl && ns_out && which >= 0 && which <= 2, "bad argument");
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const int n = std::min(std::min(g.n_strips * g.n_chunks(), pl->last_tiles), max_entries);
+    if (n > 0)
+        MCP_CUDA_TRY(cudaMemcpy(ns_out, pl->tile_ns + (size_t)which * pl->partials_cap_tiles, (size_t)n * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost));
+    return n;
+}
+
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* pl, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
                            int max_entries) {
     MCP_REQUIRE(pl && ns_out, "null argument");

@@ -56,6 +56,23 @@ def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
 
+class PendingResult:
+    """Result of a solve that has been enqueued but not waited for (:meth:`Solver.run_async`): the kernel status and
+    the global residual of the last generation travel back in one asynchronous 32-byte copy; :meth:`wait` blocks on
+    its event only.  Lets a host loop enqueue step i+1 before it looks at step i, so that the ranks' launches do not
+    drift apart by a host round trip per step."""
+
+    def __init__(self, solver, slot, event, stats, value=None):
+        self._solver, self._slot, self._event, self.stats, self._value = solver, slot, event, stats, value
+
+    def wait(self) -> Optional[float]:
+        if self._event is not None:
+            self._event.synchronize()
+            self._event = None
+            self._value = self._solver._decode_result(self._slot, self.stats)
+        return self._value
+
+
 class Solver:
     """Distributed stencil solver.  Use as a context manager or call :meth:`close`."""
 
@@ -271,12 +288,12 @@ class Solver:
         self._plan = plan
         self._desc = d
         # plan options: explicit (cfg.extra), no environment lookups inside the native library
-        for key, opt in (("timeout_ms", 1), ("debug_flags", 2), ("sync_mode", 3)):
+        for key, opt in (("timeout_ms", 1), ("debug_flags", 2), ("sync_mode", 3), ("prefetch", 4)):
             if cfg.extra.get(key) is not None:
                 _lib.check(self._lib.mcp_fused2d_set_option(plan, opt, int(cfg.extra[key])), "mcp_fused2d_set_option")
         # one pinned 32-byte block for (status, stop word, sweeps done, last residual): read back with one async copy
-        self._result_host = torch.zeros(4, dtype=torch.float64).pin_memory()
-        self._result_event = torch.cuda.Event()
+        self._result_pool = torch.zeros((8, 4), dtype=torch.float64).pin_memory()
+        self._result_next = 0
 
     # ------------------------------------------------------------------ initial condition
     def initialize(self, field: Optional[np.ndarray] = None) -> None:
@@ -394,13 +411,22 @@ class Solver:
         if getattr(self, "_stage_buf", None) is None:
             self._stage_buf = torch.empty(self.store_shape, dtype=self.tdtype, device=self.ctx.device)
             self._copy_stream = torch.cuda.Stream(device=self.ctx.device)
-            self._stage_done = torch.cuda.Event()
+            self._stage_done = torch.cuda.Event(enable_timing=True)
+            self._stage_begin = torch.cuda.Event(enable_timing=True)
             self._stage_free = torch.cuda.Event()
             self._stage_free.record()
         self._copy_stream.wait_event(self._stage_free)          # previous commit has consumed the staging buffer
         with torch.cuda.stream(self._copy_stream):
+            self._stage_begin.record(self._copy_stream)
             self._stage_buf.copy_(local, non_blocking=True)
             self._stage_done.record(self._copy_stream)
+
+    def last_upload_ms(self) -> Optional[float]:
+        """Device time of the last completed :meth:`stage_input` copy (host -> device), or None."""
+        if getattr(self, "_stage_buf", None) is None:
+            return None
+        self._stage_done.synchronize()
+        return float(self._stage_begin.elapsed_time(self._stage_done))
 
     def commit_input(self) -> None:
         """Make the staged slab the current state (device-to-device copy once the upload has landed)."""
@@ -515,23 +541,56 @@ class Solver:
         elif residual:
             self._collect_fused_residual(st)
 
-    def _collect_final_residual(self, st: RunStats) -> None:
-        """Status + global residual of the run's last generation: one asynchronous 32-byte copy into pinned memory
-        and one event, no blocking library call."""
+    def _enqueue_result(self, st: RunStats) -> PendingResult:
+        """One asynchronous 32-byte copy of the plan's result block into a pinned slot + one event."""
         from .ops import _lib
-        _lib.check(self._lib.mcp_fused2d_result_async(self._plan, self._result_host.data_ptr(), self._stream()),
+        slot = self._result_pool[self._result_next % self._result_pool.shape[0]]
+        self._result_next += 1
+        _lib.check(self._lib.mcp_fused2d_result_async(self._plan, slot.data_ptr(), self._stream()),
                    "mcp_fused2d_result_async")
-        self._result_event.record(torch.cuda.current_stream(self.ctx.device))
-        self._result_event.synchronize()
-        words = self._result_host.view(torch.int32)
-        status = int(words[0])
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.ctx.device))
+        return PendingResult(self, slot, ev, st)
+
+    def _decode_result(self, slot: torch.Tensor, st: RunStats) -> float:
+        from .ops import _lib
+        status = int(slot.view(torch.int32)[0])
         if status != 0:
             raise _lib.NativeError(f"fused kernel recorded status {status}"
                                    + (" (a flag / barrier / TMA wait timed out)" if status == -4 else ""))
-        ss, mx = float(self._result_host[2]), float(self._result_host[3])
+        ss, mx = float(slot[2]), float(slot[3])
         self._last_residual = (ss, mx)
         kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
-        st.residual_history = [(-1, float(np.sqrt(ss)) if kind == "l2" else mx)]
+        r = float(np.sqrt(ss)) if kind == "l2" else mx
+        st.residual_history = [(-1, r)]
+        return r
+
+    def _collect_final_residual(self, st: RunStats) -> None:
+        """Status + global residual of the run's last generation: one asynchronous 32-byte copy into pinned memory
+        and one event, no blocking library call."""
+        self._enqueue_result(st).wait()
+
+    def run_async(self, generations: Optional[int] = None) -> PendingResult:
+        """Enqueue a solve of ``generations`` generations (one launch, fused residual of the last generation) and
+        return without waiting; ``.wait()`` on the returned handle yields the global residual and raises if the kernel
+        recorded an error.  Up to 8 solves may be pending.  Backends without an in-kernel residual run synchronously."""
+        g = self.cfg.generations if generations is None else int(generations)
+        fused2d = self.backend == "fused" and self.ndim == 2
+        if fused2d:
+            self._ensure_plan()
+        if not fused2d or (self.ctx.distributed and not self._res_in_kernel) or g <= 0:
+            st = self.run(g, residual="final", timed=False)
+            return PendingResult(self, None, None, st, st.residual_history[-1][1] if st.residual_history else None)
+        from .ops import _lib
+        st = RunStats(generations=g, cells=self.cfg.cells)
+        before = self._lib.mcp_fused2d_launches(self._plan)
+        _lib.check(self._lib.mcp_fused2d_run(self._plan, g, self.time_block, 2, self._stream()), "mcp_fused2d_run")
+        st.launches = int(self._lib.mcp_fused2d_launches(self._plan) - before)
+        self.cur = self._lib.mcp_fused2d_parity(self._plan)
+        self.generation += g
+        self.total_stats.generations += g
+        self.total_stats.launches += st.launches
+        return self._enqueue_result(st)
 
     def _collect_fused_residual(self, st: RunStats) -> None:
         buf = (C.c_double * (2 * 16384))()
