@@ -239,12 +239,31 @@ typedef struct mcp_fused3d_desc {
     int expect[4];        /* arrivals per generation expected from each neighbour (mcp_fused3d_face_tiles) */
     double coeff;         /* diffusion number, 1/6 = 3-D stability limit */
     int zchunk;           /* planes per tile (0 = 64) */
+    /* Fused global residual all-reduce over NVLink, as in mcp_fused2d_desc (world <= 1 or res_inbox == NULL = local). */
+    int world, rank;
+    double* res_inbox;
+    uint64_t* res_flag;
+    double* peer_res_inbox[MCP_MAX_RANKS];
+    uint64_t* peer_res_flag[MCP_MAX_RANKS];
 } mcp_fused3d_desc;
 typedef struct mcp_fused3d_plan mcp_fused3d_plan;
 int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out);
 /* Tiles of a block that touch its z-, z+, y-, y+ faces: what a neighbour must expect per generation. */
 int mcp_fused3d_face_tiles(int nz, int ny, int w, int dtype, int zchunk, int* counts4);
 int mcp_fused3d_run(mcp_fused3d_plan* plan, int generations, void* stream);
+/* Same with the fused residual: MCP_RES_LAST = (sum of squares, max abs) of u' - u of EVERY generation (history read
+ * with mcp_fused3d_residuals), MCP_RES_FINAL = of the last generation only; reduced per tile, in fixed order by one
+ * warp behind the device-side grid barrier, then all-reduced over the peers' inboxes.  One launch. */
+int mcp_fused3d_run_residual(mcp_fused3d_plan* plan, int generations, int residual_mode, void* stream);
+/* Run-to-tolerance in ONE launch (stop decision on the device, identical on every rank; the run ends one generation
+ * after the one that converged).  Synchronises the stream.  Extension: the reference is 2-D with a fixed count. */
+int mcp_fused3d_run_to_tolerance(mcp_fused3d_plan* plan, int max_generations, int norm, double tol, int* generations_done,
+                                 void* stream);
+int mcp_fused3d_stop_reason(const mcp_fused3d_plan* plan);
+int mcp_fused3d_residuals(mcp_fused3d_plan* plan, double* sumsq_max_pairs, int max_entries);
+/* One asynchronous 32-byte copy of { int32 status, stop_word, gens_done, pad; double last_sumsq, last_max }. */
+int mcp_fused3d_result_async(mcp_fused3d_plan* plan, void* host32, void* stream);
+int mcp_fused3d_set_timeout_ms(mcp_fused3d_plan* plan, long long ms);
 int mcp_fused3d_parity(const mcp_fused3d_plan* plan);
 int mcp_fused3d_set_parity(mcp_fused3d_plan* plan, int parity);
 int mcp_fused3d_status(mcp_fused3d_plan* plan);

@@ -51,6 +51,9 @@ class Fused3dDesc(C.Structure):
         ("buf", C.c_void_p * 2), ("nbr_buf", (C.c_void_p * 2) * 4), ("nbr_n", C.c_int * 4),
         ("flags", C.c_void_p), ("nbr_flag", C.c_void_p * 4), ("expect", C.c_int * 4),
         ("coeff", C.c_double), ("zchunk", C.c_int),
+        ("world", C.c_int), ("rank", C.c_int),
+        ("res_inbox", C.c_void_p), ("res_flag", C.c_void_p),
+        ("peer_res_inbox", C.c_void_p * 16), ("peer_res_flag", C.c_void_p * 16),
     ]
 
 
@@ -114,6 +117,12 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_fused3d_create.argtypes = [C.POINTER(Fused3dDesc), c_void_pp]
     lib.mcp_fused3d_face_tiles.argtypes = [i, i, i, i, i, C.POINTER(i)]
     lib.mcp_fused3d_run.argtypes = [vp, i, vp]
+    lib.mcp_fused3d_run_residual.argtypes = [vp, i, i, vp]
+    lib.mcp_fused3d_run_to_tolerance.argtypes = [vp, i, i, dbl, C.POINTER(i), vp]
+    lib.mcp_fused3d_stop_reason.argtypes = [vp]
+    lib.mcp_fused3d_residuals.argtypes = [vp, vp, i]
+    lib.mcp_fused3d_result_async.argtypes = [vp, vp, vp]
+    lib.mcp_fused3d_set_timeout_ms.argtypes = [vp, C.c_longlong]
     lib.mcp_fused3d_parity.argtypes = [vp]
     lib.mcp_fused3d_set_parity.argtypes = [vp, i]
     lib.mcp_fused3d_status.argtypes = [vp]

@@ -11,8 +11,11 @@
 // Compute scheme (2.5-D blocking): a CTA owns a tile of 32 rows x 128 columns (fp64: 64) and marches along z over
 // a chunk of planes.  TMA (cp.async.bulk.tensor.3d) streams (32+2) x (128+8) boxes of successive planes into a
 // 4-slot shared-memory ring with mbarrier completion; each thread keeps its 4 rows x 16 bytes of the planes
-// z-1, z, z+1 in registers, so a plane is read from shared memory once.  One generation per pass (no temporal
+// z-1, z, z+1 in registers, so a plane is read from shared memory once (plus the two neighbour cells of a lane's
+// vector).  One generation per pass (no temporal
 // blocking: the 3-D working set does not fit the register file), device-side grid barrier between generations.
+// Optional fused residual: per-tile (sum d^2, max |d|) -> fixed-order reduction by CTA 0 behind the grid barrier ->
+// all-reduce over the peers' inboxes (NVLink), history + stop decision on the device (run-to-tolerance in one launch).
 // Arithmetic: oracle.heat3d_update_cells, every operation individually rounded.
 #include <algorithm>
 #include <new>
@@ -34,6 +37,18 @@ constexpr int k3Slots = 4;
 constexpr int k3BoxBytes = k3BoxRows * k3RowBytes;             // 18496 bytes delivered by one TMA box
 constexpr int k3SlotBytes = (k3BoxBytes + 127) / 128 * 128;   // ring slots stay 128-byte aligned for TMA
 constexpr int k3SmemBytes = k3Slots * k3SlotBytes + 64;
+constexpr int k3MaxRanks = MCP_MAX_RANKS;
+constexpr int k3ResRing = MCP_RES_RING;
+constexpr int k3MaxResSlots = 16384;
+
+// One 32-byte block per plan that a host reads back with ONE copy after a run (same layout as the 2-D kernel's).
+struct Result3d {
+    int status;       // 0 or the MCP_ERR_* code a kernel recorded
+    int stop_word;    // run-to-tolerance: 0 = keep going, else the number of generations this launch executes
+    int gens_done;    // generations actually executed by the last launch
+    int pad;
+    double last_sumsq, last_max;
+};
 
 struct Fused3dParams {
     void* buf[2];
@@ -56,6 +71,17 @@ struct Fused3dParams {
     int n_tiles, zchunk;
     int generations, first_parity;
     double coeff;
+    // fused residual (generations >= res_first_gen accumulate it)
+    int res_first_gen, res_slot0, stop_mode;
+    double stop_thresh;
+    double* partials;  // [2][n_tiles][2]
+    double* res_out;   // [k3MaxResSlots][2]
+    Result3d* result;
+    int world, rank;
+    double* peer_inbox[k3MaxRanks];
+    unsigned long long* peer_res_flag[k3MaxRanks];
+    const unsigned long long* res_flag;
+    unsigned long long res_seq_base;
 };
 
 __device__ __forceinline__ bool aborted3(const Fused3dParams& p) { return *((volatile int*)p.status) != 0; }
@@ -91,7 +117,89 @@ struct V3<double> {
     static constexpr int VEC = 2;
 };
 
-template <class T>
+// v = *p (shared memory) if pred, else v unchanged; one predicated LDS, no branch.
+__device__ __forceinline__ void ld_shared_if(float& v, const float* p, bool pred) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q ld.shared.f32 %0, [%1];\n\t}"
+                 : "+f"(v) : "r"(ptx::smem_u32(p)), "r"((int)pred) : "memory");
+}
+__device__ __forceinline__ void ld_shared_if(double& v, const double* p, bool pred) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q ld.shared.f64 %0, [%1];\n\t}"
+                 : "+d"(v) : "r"(ptx::smem_u32(p)), "r"((int)pred) : "memory");
+}
+
+__device__ __forceinline__ void accum3(const float4& a, const float4& b, double& ss, double& mx) {
+    // differences and squares in fp32 (the field's precision), one conversion per vector, fp64 across vectors
+    const float d0 = __fsub_rn(a.x, b.x), d1 = __fsub_rn(a.y, b.y), d2 = __fsub_rn(a.z, b.z), d3 = __fsub_rn(a.w, b.w);
+    float q = __fmul_rn(d0, d0);
+    q = __fmaf_rn(d1, d1, q);
+    q = __fmaf_rn(d2, d2, q);
+    q = __fmaf_rn(d3, d3, q);
+    ss += (double)q;
+    mx = fmax(mx, (double)fmaxf(fmaxf(fabsf(d0), fabsf(d1)), fmaxf(fabsf(d2), fabsf(d3))));
+}
+__device__ __forceinline__ void accum3(const double2& a, const double2& b, double& ss, double& mx) {
+    const double d0 = a.x - b.x, d1 = a.y - b.y;
+    ss = fma(d0, d0, ss);
+    ss = fma(d1, d1, ss);
+    mx = fmax(mx, fmax(fabs(d0), fabs(d1)));
+}
+
+// Fixed-order reduction of one generation's per-tile partials by ONE warp, the all-reduce over the peers' inboxes,
+// the residual history, the result block and the stop decision (same protocol as the 2-D kernel).
+__device__ __noinline__ void reduce_and_exchange3(const Fused3dParams& p, const double* partials, const int gen,
+                                                  const int lane) {
+    double a = 0.0, b = 0.0;
+    for (int i = lane; i < p.n_tiles; i += 32) {
+        a += __ldcg(&partials[2 * i]);
+        b = fmax(b, __ldcg(&partials[2 * i + 1]));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b = fmax(b, __shfl_xor_sync(0xffffffffu, b, o));
+    }
+    if (lane == 0) {
+        double sa = a, sb = b;
+        if (p.world > 1 && p.peer_inbox[0] != nullptr) {
+            const unsigned long long seq = p.res_seq_base + (unsigned long long)(gen - p.res_first_gen);
+            const size_t off = ((size_t)(seq % k3ResRing) * k3MaxRanks + (size_t)p.rank) * 2;
+            for (int r = 0; r < p.world; ++r) {
+                p.peer_inbox[r][off] = sa;
+                p.peer_inbox[r][off + 1] = sb;
+            }
+            ptx::fence_acq_rel_sys();
+            for (int r = 0; r < p.world; ++r) ptx::red_add_relaxed_sys(p.peer_res_flag[r], 1ull);
+            if (wait_ctr3(p, p.res_flag, (seq + 1ull) * (unsigned long long)p.world, true)) {
+                const volatile double* in = p.peer_inbox[p.rank] + (size_t)(seq % k3ResRing) * k3MaxRanks * 2;
+                sa = 0.0;
+                sb = 0.0;
+                for (int r = 0; r < p.world; ++r) {  // rank order: the same bits on every rank
+                    sa += in[2 * r];
+                    sb = fmax(sb, in[2 * r + 1]);
+                }
+            }
+        }
+        const int slot = p.res_slot0 + (gen - p.res_first_gen);
+        if (slot < k3MaxResSlots) {
+            p.res_out[2 * slot] = sa;
+            p.res_out[2 * slot + 1] = sb;
+        }
+        p.result->last_sumsq = sa;
+        p.result->last_max = sb;
+        if (p.stop_mode != 0 && *((volatile int*)&p.result->stop_word) == 0) {
+            const bool conv = p.stop_mode == 1 ? (sb <= p.stop_thresh) : (sa <= p.stop_thresh);
+            if (conv) {
+                *((volatile int*)&p.result->stop_word) = gen + 2;  // one more generation runs while this is published
+                __threadfence();
+            }
+        }
+    }
+    __syncwarp();
+}
+
+// RESK: the instantiation that can accumulate the residual (launched only when a residual is asked for, so that the
+// plain kernel keeps its registers for the planes).
+template <class T, bool RESK>
 __global__ void __launch_bounds__(k3Threads, 2)
 heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ Fused3dParams p) {
@@ -103,6 +211,7 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + k3Slots * k3SlotBytes);
     __shared__ int s_ticket, s_ok;
+    __shared__ double s_red[2][k3Threads / 32];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
@@ -117,7 +226,15 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     unsigned long long epoch = 0;
     const T coeff = (T)p.coeff;
 
+    int executed = 0;
     for (int gen = 0; gen < p.generations; ++gen) {
+        const bool res_now = RESK && gen >= p.res_first_gen;
+        if (RESK && p.stop_mode != 0 && gen > 0) {
+            // decided from the global residual of generation gen-2 and published before barrier gen-1
+            const int sgen = *((volatile int*)&p.result->stop_word);
+            if (sgen != 0 && gen >= sgen) break;
+        }
+        double* partials = p.partials + (size_t)(gen & 1) * p.n_tiles * 2;
         const int par = (p.first_parity + gen) & 1;
         const CUtensorMap* tm_in = par ? &tmB : &tmA;
         T* out = reinterpret_cast<T*>(p.buf[par ^ 1]);
@@ -204,8 +321,10 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
             // GEN = the tile touches a pencil face (halo pushes) or holds fixed cells (masks); interior tiles
             // run the lean instantiation: no masks, no push tests, unconditional stores.
-            auto zloop = [&](auto gen_tag) {
+            double rs = 0.0, rm = 0.0;
+            auto zloop = [&](auto gen_tag, auto res_tag) {
             constexpr bool GEN = decltype(gen_tag)::value;
+            constexpr bool RES = decltype(res_tag)::value;
             for (int s = 0; s < zhi - zlo; ++s) {
                 const int pz = zlo + s;                // plane being computed
                 const uint32_t uC = use + 1 + s, uD = use + 2 + s;
@@ -217,8 +336,20 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const T* cw = reinterpret_cast<const T*>(rowC + (r0 + i + 1) * k3RowBytes + colb);
-                    const T wl = cw[-1], er = cw[VEC];
                     const T* pc = reinterpret_cast<const T*>(&Cc[i + 1]);
+                    // West / east neighbours of the lane's vector.  Measured on B200 (profiles/r2/heat3d_neighbours.md):
+                    // reading them from the box in shared memory (a 4-way bank conflict, 26 M conflicts per launch)
+                    // is 5 % FASTER than taking them from the adjacent lanes with shuffles + predicated halo loads
+                    // for lanes 0 / 31 (442 K conflicts): the kernel is bound by barriers and latency, not by
+                    // shared-memory bandwidth, and the shuffles cost issue slots.  The shuffle form stays selectable.
+#ifndef MCP_H3_SHUFFLE_NEIGHBOURS
+                    const T wl = cw[-1], er = cw[VEC];
+#else
+                    T wl = __shfl_up_sync(0xffffffffu, pc[VEC - 1], 1);
+                    T er = __shfl_down_sync(0xffffffffu, pc[0], 1);
+                    ld_shared_if(wl, cw - 1, lane == 0);    // predicated loads: no divergent branch in the plane loop
+                    ld_shared_if(er, cw + VEC, lane == 31);
+#endif
                     const T* pn = reinterpret_cast<const T*>(&Cc[i]);
                     const T* ps = reinterpret_cast<const T*>(&Cc[i + 2]);
                     const T* pu = reinterpret_cast<const T*>(&U[i]);
@@ -234,6 +365,7 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         po[k] = (GEN && (rfix || ((xfix >> k) & 1u))) ? pc[k] : v;
                     }
                     if (!GEN || ((ystore >> i) & 1u)) {
+                        if (RES) accum3(o, Cc[i + 1], rs, rm);
                         const int ly = ylo + r0 + i;
                         uint4 bits;
                         memcpy(&bits, &o, 16);
@@ -265,12 +397,41 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const bool lean = !f_zm && !f_zp && !f_ym && !f_yp && (p.z0 + zlo >= 1) && (p.z0 + zhi - 1 <= p.d - 2) &&
                               (p.y0 + ylo >= 1) && (p.y0 + ylo + k3TileRows - 1 <= p.h - 2) && (x0 >= 1) &&
                               (x0 + XS - 1 <= p.w - 2);
-            if (lean) zloop(std::false_type{}); else zloop(std::true_type{});
+            bool did_res = false;
+            if constexpr (RESK) {
+                if (res_now) {
+                    did_res = true;
+                    if (lean) zloop(std::false_type{}, std::true_type{}); else zloop(std::true_type{}, std::true_type{});
+                }
+            }
+            if (!did_res) {
+                if (lean) zloop(std::false_type{}, std::false_type{}); else zloop(std::true_type{}, std::false_type{});
+            }
             use += n_planes;
+            if (res_now) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    rs += __shfl_xor_sync(0xffffffffu, rs, o);
+                    rm = fmax(rm, __shfl_xor_sync(0xffffffffu, rm, o));
+                }
+                if (lane == 0) {
+                    s_red[0][warp] = rs;
+                    s_red[1][warp] = rm;
+                }
+            }
 
             // publish the pushed halo layers: all threads' peer stores -> one release per face
             __syncthreads();
             if (tid == 0) {
+                if (res_now) {  // warp order: the same bits whichever CTA ran the tile
+                    double a = 0.0, b = 0.0;
+                    for (int k = 0; k < k3Threads / 32; ++k) {
+                        a += s_red[0][k];
+                        b = fmax(b, s_red[1][k]);
+                    }
+                    partials[2 * q] = a;
+                    partials[2 * q + 1] = b;
+                }
                 const bool touch[4] = {f_zm, f_zp, f_ym, f_yp};
                 bool fenced = false;  // one system-scope fence (a round trip to the peers), then relaxed signals
                 for (int f = 0; f < 4; ++f)
@@ -282,8 +443,8 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
         }
 
-        if (gen + 1 < p.generations) {
-            // grid barrier between generations
+        if (res_now || gen + 1 < p.generations) {
+            // grid barrier between generations (and in front of the reduction of a residual generation)
             __syncthreads();
             if (tid == 0) {
                 ptx::fence_proxy_async();
@@ -297,7 +458,13 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             ++epoch;
         }
         if (aborted3(p)) break;
+        if (res_now && blockIdx.x == 0) {
+            if (warp == 0) reduce_and_exchange3(p, partials, gen, lane);
+            __syncthreads();
+        }
+        executed = gen + 1;
     }
+    if (blockIdx.x == 0 && tid == 0) p.result->gens_done = executed;
 }
 
 }  // namespace mcp
@@ -308,10 +475,13 @@ struct mcp_fused3d_plan {
     mcp_fused3d_desc d;
     CUtensorMap tm[2];
     unsigned long long* grid_bar;
-    int* status;
+    Result3d* result;
+    double* partials;
+    double* res_out;
     int* tiles_dev;
     int n_tiles, zchunk, grid, parity;
-    unsigned long long flag_base[4], bar_base, ctr_base;
+    unsigned long long flag_base[4], bar_base, ctr_base, res_seq, timeout_ns;
+    int res_slots_used, last_generations, last_stop_reason;
     int64_t launches;
 };
 
@@ -348,8 +518,14 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
     pl->bar_base = pl->ctr_base = 0;
     for (int f = 0; f < 4; ++f) pl->flag_base[f] = 0;
     pl->grid_bar = nullptr;
-    pl->status = nullptr;
+    pl->result = nullptr;
+    pl->partials = nullptr;
+    pl->res_out = nullptr;
     pl->tiles_dev = nullptr;
+    pl->res_seq = 0;
+    pl->timeout_ns = 20ull * 1000000000ull;
+    pl->res_slots_used = pl->last_generations = 0;
+    pl->last_stop_reason = MCP_STOP_NONE;
     int sm = 0;
     int rc = device_sm_count(&sm);
     if (rc) { delete pl; return rc; }
@@ -380,7 +556,10 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
     pl->n_tiles = (int)face.size();
     cudaError_t e;
     if ((e = cudaMalloc(&pl->grid_bar, 512)) != cudaSuccess || (e = cudaMemset(pl->grid_bar, 0, 512)) != cudaSuccess ||
-        (e = cudaMalloc(&pl->status, 256)) != cudaSuccess || (e = cudaMemset(pl->status, 0, 256)) != cudaSuccess ||
+        (e = cudaMalloc(&pl->result, 256)) != cudaSuccess || (e = cudaMemset(pl->result, 0, 256)) != cudaSuccess ||
+        (e = cudaMalloc(&pl->partials, face.size() * 4 * sizeof(double))) != cudaSuccess ||
+        (e = cudaMalloc(&pl->res_out, (size_t)k3MaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
+        (e = cudaMemset(pl->res_out, 0, (size_t)k3MaxResSlots * 2 * sizeof(double))) != cudaSuccess ||
         (e = cudaMalloc(&pl->tiles_dev, face.size() * sizeof(int))) != cudaSuccess ||
         (e = cudaMemcpy(pl->tiles_dev, face.data(), face.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess) {
         set_error("mcp_fused3d_create: scratch allocation failed: %s", cudaGetErrorString(e));
@@ -397,10 +576,16 @@ int mcp_fused3d_face_tiles(int nz, int ny, int w, int dtype, int zchunk, int* co
     return MCP_OK;
 }
 
-int mcp_fused3d_run(mcp_fused3d_plan* pl, int generations, void* stream_) {
-    MCP_REQUIRE(pl && generations >= 0, "mcp_fused3d_run: bad arguments");
-    if (generations == 0) return MCP_OK;
+static int run3d_impl(mcp_fused3d_plan* pl, int generations, int residual_mode, int stop_mode, double stop_thresh,
+                      cudaStream_t stream) {
     const mcp_fused3d_desc& d = pl->d;
+    pl->last_generations = 0;
+    pl->last_stop_reason = MCP_STOP_NONE;
+    if (residual_mode != MCP_RES_NONE) pl->res_slots_used = 0;
+    if (generations == 0) return MCP_OK;
+    const int requested = generations;
+    if (stop_mode != 0) generations = std::min(generations, k3MaxResSlots);
+    const bool exchange = d.world > 1 && d.res_inbox != nullptr;
     Fused3dParams p;
     memset(&p, 0, sizeof(p));
     for (int b = 0; b < 2; ++b) {
@@ -418,8 +603,9 @@ int mcp_fused3d_run(mcp_fused3d_plan* pl, int generations, void* stream_) {
     p.tile_ctr = pl->grid_bar + 16;
     p.bar_base = pl->bar_base;
     p.ctr_base = pl->ctr_base;
-    p.timeout_ns = 20ull * 1000000000ull;
-    p.status = pl->status;
+    p.timeout_ns = pl->timeout_ns;
+    p.result = pl->result;
+    p.status = &pl->result->status;
     p.tiles = pl->tiles_dev;
     p.pitch = d.pitch;
     p.plane_pitch = d.pitch * d.py_alloc;
@@ -433,21 +619,113 @@ int mcp_fused3d_run(mcp_fused3d_plan* pl, int generations, void* stream_) {
     p.generations = generations;
     p.first_parity = pl->parity;
     p.coeff = d.coeff;
+    // MCP_RES_LAST: every generation carries the residual; MCP_RES_FINAL: only the last one
+    p.res_first_gen = residual_mode == MCP_RES_LAST ? 0 : (residual_mode == MCP_RES_FINAL ? generations - 1 : generations);
+    p.res_slot0 = pl->res_slots_used;
+    p.stop_mode = stop_mode;
+    p.stop_thresh = stop_thresh;
+    p.partials = pl->partials;
+    p.res_out = pl->res_out;
+    p.world = d.world > 0 ? d.world : 1;
+    p.rank = d.rank;
+    p.res_flag = (const unsigned long long*)d.res_flag;
+    p.res_seq_base = pl->res_seq;
+    if (exchange)
+        for (int r = 0; r < p.world; ++r) {
+            p.peer_inbox[r] = (double*)d.peer_res_inbox[r];
+            p.peer_res_flag[r] = (unsigned long long*)d.peer_res_flag[r];
+        }
+    if (stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(&pl->result->stop_word, 0, 2 * sizeof(int), stream));
 
     void* args[3] = {(void*)&pl->tm[0], (void*)&pl->tm[1], (void*)&p};
-    const void* fn = d.dtype == MCP_DTYPE_F64 ? (const void*)heat3d_fused_kernel<double>
-                                              : (const void*)heat3d_fused_kernel<float>;
+    const bool resk = residual_mode != MCP_RES_NONE;
+    const void* fn = d.dtype == MCP_DTYPE_F64
+                         ? (resk ? (const void*)heat3d_fused_kernel<double, true> : (const void*)heat3d_fused_kernel<double, false>)
+                         : (resk ? (const void*)heat3d_fused_kernel<float, true> : (const void*)heat3d_fused_kernel<float, false>);
     MCP_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, k3SmemBytes));
     int per_sm = 0;
     MCP_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, k3Threads, k3SmemBytes));
     MCP_REQUIRE(per_sm >= 1, "heat3d kernel does not fit on an SM");
     const int grid = std::min(pl->grid, per_sm * (pl->grid / 2));
-    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(k3Threads), args, k3SmemBytes, (cudaStream_t)stream_));
+    MCP_CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(k3Threads), args, k3SmemBytes, stream));
     pl->launches++;
-    pl->bar_base += (unsigned long long)(generations - 1) * grid;
-    pl->ctr_base += (unsigned long long)generations * (unsigned long long)(pl->n_tiles + grid);
-    for (int f = 0; f < 4; ++f) pl->flag_base[f] += (unsigned long long)generations * d.expect[f];
-    pl->parity = (pl->parity + generations) & 1;
+
+    int executed = generations;
+    if (stop_mode != 0) {
+        // the number of generations that ran is decided on the device: wait for it before touching the counters
+        MCP_CUDA_TRY(cudaStreamSynchronize(stream));
+        Result3d rb;
+        MCP_CUDA_TRY(cudaMemcpy(&rb, pl->result, sizeof(rb), cudaMemcpyDeviceToHost));
+        executed = rb.gens_done;
+        MCP_REQUIRE(executed >= 0 && executed <= generations, "device reported %d executed generations of %d", executed,
+                    generations);
+        pl->last_stop_reason = rb.stop_word != 0 ? MCP_STOP_CONVERGED
+                                                 : (generations < requested ? MCP_STOP_SLOT_LIMIT : MCP_STOP_MAX_GENERATIONS);
+    }
+    const int res_gens = std::max(0, executed - p.res_first_gen);
+    // a barrier after every generation but the last, and after the last one too when it carries the residual
+    unsigned long long barriers = (unsigned long long)std::max(0, executed - 1);
+    if (executed > 0 && executed - 1 >= p.res_first_gen) barriers += 1;
+    pl->bar_base += barriers * grid;
+    pl->ctr_base += (unsigned long long)executed * (unsigned long long)(pl->n_tiles + grid);
+    for (int f = 0; f < 4; ++f) pl->flag_base[f] += (unsigned long long)executed * d.expect[f];
+    pl->parity = (pl->parity + executed) & 1;
+    pl->res_slots_used = std::min(k3MaxResSlots, pl->res_slots_used + res_gens);
+    if (exchange) pl->res_seq += (unsigned long long)res_gens;
+    pl->last_generations = executed;
+    return MCP_OK;
+}
+
+int mcp_fused3d_run(mcp_fused3d_plan* pl, int generations, void* stream_) {
+    MCP_REQUIRE(pl && generations >= 0, "mcp_fused3d_run: bad arguments");
+    return run3d_impl(pl, generations, MCP_RES_NONE, 0, 0.0, (cudaStream_t)stream_);
+}
+
+int mcp_fused3d_run_residual(mcp_fused3d_plan* pl, int generations, int residual_mode, void* stream_) {
+    MCP_REQUIRE(pl && generations >= 0, "mcp_fused3d_run_residual: bad arguments");
+    MCP_REQUIRE(residual_mode == MCP_RES_NONE || residual_mode == MCP_RES_LAST || residual_mode == MCP_RES_FINAL,
+                "residual_mode must be MCP_RES_NONE, MCP_RES_LAST or MCP_RES_FINAL");
+    MCP_REQUIRE(residual_mode != MCP_RES_LAST || generations <= k3MaxResSlots,
+                "at most %d generations per call with a residual history", k3MaxResSlots);
+    return run3d_impl(pl, generations, residual_mode, 0, 0.0, (cudaStream_t)stream_);
+}
+
+int mcp_fused3d_run_to_tolerance(mcp_fused3d_plan* pl, int max_generations, int norm, double tol, int* generations_done,
+                                 void* stream_) {
+    MCP_REQUIRE(pl && max_generations >= 1, "mcp_fused3d_run_to_tolerance: bad arguments");
+    MCP_REQUIRE(norm == MCP_NORM_LINF || norm == MCP_NORM_L2, "norm must be MCP_NORM_LINF or MCP_NORM_L2");
+    MCP_REQUIRE(tol >= 0.0, "negative tolerance");
+    const mcp_fused3d_desc& d = pl->d;
+    bool neighbours = false;
+    for (int f = 0; f < 4; ++f) neighbours = neighbours || d.nbr_buf[f][0] != nullptr;
+    MCP_REQUIRE(!neighbours || d.res_inbox != nullptr,
+                "run_to_tolerance across ranks needs the fused residual exchange (res_inbox): a local residual would "
+                "stop the ranks in different generations");
+    int rc = run3d_impl(pl, max_generations, MCP_RES_LAST, norm == MCP_NORM_LINF ? 1 : 2,
+                        norm == MCP_NORM_L2 ? tol * tol : tol, (cudaStream_t)stream_);
+    if (generations_done) *generations_done = pl->last_generations;
+    return rc;
+}
+
+int mcp_fused3d_stop_reason(const mcp_fused3d_plan* pl) { return pl ? pl->last_stop_reason : MCP_STOP_NONE; }
+
+int mcp_fused3d_residuals(mcp_fused3d_plan* pl, double* out, int max_entries) {
+    MCP_REQUIRE(pl && out, "null argument");
+    const int n = std::min(pl->res_slots_used, max_entries);
+    if (n > 0) MCP_CUDA_TRY(cudaMemcpy(out, pl->res_out, (size_t)n * 2 * sizeof(double), cudaMemcpyDeviceToHost));
+    return n;
+}
+
+int mcp_fused3d_result_async(mcp_fused3d_plan* pl, void* host32, void* stream_) {
+    MCP_REQUIRE(pl && host32, "null argument");
+    static_assert(sizeof(Result3d) == 32, "result block layout");
+    MCP_CUDA_TRY(cudaMemcpyAsync(host32, pl->result, sizeof(Result3d), cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+    return MCP_OK;
+}
+
+int mcp_fused3d_set_timeout_ms(mcp_fused3d_plan* pl, long long ms) {
+    MCP_REQUIRE(pl && ms >= 1, "bad timeout");
+    pl->timeout_ns = (unsigned long long)ms * 1000000ull;
     return MCP_OK;
 }
 
@@ -462,7 +740,7 @@ int mcp_fused3d_set_parity(mcp_fused3d_plan* pl, int parity) {
 int mcp_fused3d_status(mcp_fused3d_plan* pl) {
     MCP_REQUIRE(pl, "null plan");
     int st = 0;
-    MCP_CUDA_TRY(cudaMemcpy(&st, pl->status, sizeof(int), cudaMemcpyDeviceToHost));
+    MCP_CUDA_TRY(cudaMemcpy(&st, &pl->result->status, sizeof(int), cudaMemcpyDeviceToHost));
     if (st != 0) set_error("fused3d kernel recorded status %d", st);
     return st;
 }
@@ -472,7 +750,9 @@ int64_t mcp_fused3d_launches(const mcp_fused3d_plan* pl) { return pl ? pl->launc
 int mcp_fused3d_destroy(mcp_fused3d_plan* pl) {
     if (!pl) return MCP_OK;
     if (pl->grid_bar) cudaFree(pl->grid_bar);
-    if (pl->status) cudaFree(pl->status);
+    if (pl->result) cudaFree(pl->result);
+    if (pl->partials) cudaFree(pl->partials);
+    if (pl->res_out) cudaFree(pl->res_out);
     if (pl->tiles_dev) cudaFree(pl->tiles_dev);
     delete pl;
     return MCP_OK;

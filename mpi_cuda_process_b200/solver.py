@@ -225,10 +225,24 @@ class Solver:
             d.expect[f] = counts[opposite[f]]
         d.flags = self._arena.peer_ptr(self.ctx.rank, 512)
         d.coeff = oracle.HEAT3D_COEFF
+        d.world, d.rank = self.ctx.world, self.ctx.rank
+        self._res_in_kernel = False
+        if self.ctx.distributed and not cfg.extra.get("host_residual", False):
+            # same pad layout as the 2-D kernel: residual arrival counter @256, inbox ring @4096
+            d.res_inbox = self._arena.peer_ptr(self.ctx.rank, 4096)
+            d.res_flag = self._arena.peer_ptr(self.ctx.rank, 256)
+            for r in range(self.ctx.world):
+                d.peer_res_inbox[r] = self._arena.peer_ptr(r, 4096)
+                d.peer_res_flag[r] = self._arena.peer_ptr(r, 256)
+            self._res_in_kernel = True
         plan = C.c_void_p()
         _lib.check(self._lib.mcp_fused3d_create(C.byref(d), C.byref(plan)), "mcp_fused3d_create")
         self._plan = plan
         self._desc = d
+        if cfg.extra.get("timeout_ms") is not None:
+            _lib.check(self._lib.mcp_fused3d_set_timeout_ms(plan, int(cfg.extra["timeout_ms"])))
+        self._result_pool = torch.zeros((8, 4), dtype=torch.float64).pin_memory()
+        self._result_next = 0
 
     def _ensure_plan(self):
         if self._plan is not None:
@@ -459,7 +473,7 @@ class Solver:
         (the sweep kernel runs its cheaper residual-free instantiation for all but the last time block)."""
         g = self.cfg.generations if generations is None else int(generations)
         self._res_final = False
-        if residual == "final" and self.backend == "fused" and self.ndim == 2:
+        if residual == "final" and self.backend == "fused":
             self._res_final = True      # one launch: only the last time block runs the residual row loop
             residual = True
         if residual == "final":
@@ -510,18 +524,41 @@ class Solver:
 
     # -- fused ---------------------------------------------------------------------------------
     def _run_fused3d(self, g: int, residual: bool, st: RunStats) -> None:
+        """One launch; the residual (every generation, or the last one for residual="final") is accumulated by the
+        sweep kernel itself and all-reduced over NVLink -- no second pass over the field, no host-side reduction."""
         from .ops import _lib
         self._ensure_plan()
-        n = g - 1 if residual else g          # the residual needs both generations: last step separately
         before = self._lib.mcp_fused3d_launches(self._plan)
-        if n > 0:
-            _lib.check(self._lib.mcp_fused3d_run(self._plan, n, self._stream()), "mcp_fused3d_run")
-        if residual:
-            prev = self._lib.mcp_fused3d_parity(self._plan)
-            _lib.check(self._lib.mcp_fused3d_run(self._plan, 1, self._stream()), "mcp_fused3d_run")
-            cur = self._lib.mcp_fused3d_parity(self._plan)
-            self.cur = cur
-            self._record_residual(st, self.bufs[prev], self.bufs[cur])
+        in_kernel = residual and (self._res_in_kernel or not self.ctx.distributed)
+        if in_kernel:
+            final = getattr(self, "_res_final", False)
+            done = 0
+            hist = []
+            while done < g:                                    # the device history holds 16384 generations per call
+                n = g - done if final else min(g - done, 16384)
+                _lib.check(self._lib.mcp_fused3d_run_residual(self._plan, n, 2 if final else 1, self._stream()),
+                           "mcp_fused3d_run_residual")
+                buf = (C.c_double * (2 * 16384))()
+                k = _lib.check(self._lib.mcp_fused3d_residuals(self._plan, buf, 16384), "mcp_fused3d_residuals")
+                hist += [(buf[2 * i], buf[2 * i + 1]) for i in range(k)]
+                done += n
+            _lib.check(self._lib.mcp_fused3d_status(self._plan), "fused kernel status")
+            kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+            if hist:
+                self._last_residual = hist[-1]
+            base = self.generation + (g - len(hist))
+            st.residual_history = [(base + i + 1, float(np.sqrt(ss)) if kind == "l2" else mx)
+                                   for i, (ss, mx) in enumerate(hist)]
+        else:
+            n = g - 1 if residual else g          # host residual (extra={"host_residual": True}): last step apart
+            if n > 0:
+                _lib.check(self._lib.mcp_fused3d_run(self._plan, n, self._stream()), "mcp_fused3d_run")
+            if residual:
+                prev = self._lib.mcp_fused3d_parity(self._plan)
+                _lib.check(self._lib.mcp_fused3d_run(self._plan, 1, self._stream()), "mcp_fused3d_run")
+                cur = self._lib.mcp_fused3d_parity(self._plan)
+                self.cur = cur
+                self._record_residual(st, self.bufs[prev], self.bufs[cur])
         st.launches = int(self._lib.mcp_fused3d_launches(self._plan) - before)
         self.cur = self._lib.mcp_fused3d_parity(self._plan)
 
@@ -827,6 +864,10 @@ class Solver:
             every = max(self.time_block, every // self.time_block * self.time_block)
         total = RunStats(cells=self.cfg.cells)
         kind = self.cfg.residual if self.cfg.residual != "none" else "linf"
+        if self.backend == "fused" and self.ndim == 3 and not self.cfg.extra.get("host_tolerance_loop", False):
+            self._ensure_plan()
+            if not self.ctx.distributed or self._res_in_kernel:
+                return self._run_to_tolerance_fused3d(tol, max_g, kind)
         if self.backend == "fused" and self.ndim == 2 and not self.cfg.extra.get("host_tolerance_loop", False):
             self._ensure_plan()
             if self.ctx.distributed and self.cfg.extra.get("residual_allreduce") == "nvls" and kind == "l2":
@@ -895,6 +936,43 @@ class Solver:
             st.stop_reason = {1: "converged", 2: "max_generations", 3: "slot_limit"}.get(
                 int(self._lib.mcp_fused2d_stop_reason(self._plan)), "")
             # "slot_limit": the history table filled up before the tolerance was met -- not converged, go on
+            if st.stop_reason != "slot_limit" or st.generations >= max_g or done.value <= 0:
+                break
+        self.generation += st.generations
+        self.total_stats.generations += st.generations
+        self.total_stats.device_ms += st.device_ms
+        self.total_stats.launches += st.launches
+        return st
+
+    def _run_to_tolerance_fused3d(self, tol: float, max_g: int, kind: str) -> RunStats:
+        """3-D: the sweep kernel all-reduces the residual of every generation and stops itself (one launch per 16384
+        generations)."""
+        from .ops import _lib
+        st = RunStats(cells=self.cfg.cells)
+        while True:
+            done = C.c_int(0)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            before = self._lib.mcp_fused3d_launches(self._plan)
+            ev0.record()
+            _lib.check(self._lib.mcp_fused3d_run_to_tolerance(self._plan, max_g - st.generations,
+                                                              2 if kind == "l2" else 1, float(tol), C.byref(done),
+                                                              self._stream()), "mcp_fused3d_run_to_tolerance")
+            ev1.record()
+            ev1.synchronize()
+            st.device_ms += self.ctx.all_reduce_max(ev0.elapsed_time(ev1))
+            st.launches += int(self._lib.mcp_fused3d_launches(self._plan) - before)
+            self.cur = self._lib.mcp_fused3d_parity(self._plan)
+            _lib.check(self._lib.mcp_fused3d_status(self._plan), "fused kernel status")
+            buf = (C.c_double * (2 * 16384))()
+            k = _lib.check(self._lib.mcp_fused3d_residuals(self._plan, buf, 16384), "mcp_fused3d_residuals")
+            base = self.generation + st.generations
+            st.residual_history += [(base + i + 1, float(np.sqrt(buf[2 * i])) if kind == "l2" else buf[2 * i + 1])
+                                    for i in range(k)]
+            if k:
+                self._last_residual = (buf[2 * (k - 1)], buf[2 * (k - 1) + 1])
+            st.generations += int(done.value)
+            st.stop_reason = {1: "converged", 2: "max_generations", 3: "slot_limit"}.get(
+                int(self._lib.mcp_fused3d_stop_reason(self._plan)), "")
             if st.stop_reason != "slot_limit" or st.generations >= max_g or done.value <= 0:
                 break
         self.generation += st.generations

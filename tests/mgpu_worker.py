@@ -88,6 +88,29 @@ def main() -> int:
                 print(json.dumps({"case": "fused residual", "world": ctx.world, "equal_on_all_ranks": ok}), flush=True)
             if not ok:
                 rc = 1
+    # 3-D: residual of every generation from the sweep kernel, all-reduced over NVLink; identical on all ranks
+    if rc == 0:
+        for decomp in ("slab", "pencil"):
+            if decomp == "pencil" and ctx.world < 4:
+                continue
+            cfg = RunConfig(workload="heat3d", depth=43, height=77, width=260, backend="fused", residual="linf",
+                            decomposition=decomp)
+            with Solver(cfg, ctx=ctx) as s:
+                s.initialize()
+                st = s.run(7, residual=True)
+                s.check_status()
+                u = oracle.heat3d_init(43, 77, 260)
+                exp = []
+                for _ in range(7):
+                    v = oracle.heat3d_step(u)
+                    exp.append(oracle.residual(v, u, "linf"))
+                    u = v
+                got = [r for _, r in st.residual_history]
+                ok = all(a == exp for a in ctx.all_gather_object(got)) and st.launches == 1
+                if ctx.rank == 0:
+                    print(json.dumps({"case": f"heat3d fused residual ({decomp})", "world": ctx.world, "ok": bool(ok)}), flush=True)
+                if not ok:
+                    rc = 1
     # run-to-tolerance in one launch, decision taken on the device from the NVLink all-reduce (fp64, l2 norm)
     if rc == 0:
         cfg = RunConfig(workload="mdf", height=96, width=80, backend="fused", time_block=4, dtype="fp64",

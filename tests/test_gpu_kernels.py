@@ -361,3 +361,52 @@ def test_final_residual_single_launch_matches_history():
         hist = s.run(40, residual=True).residual_history
     u = oracle.mdf_run(oracle.mdf_init(200, 300), 39)
     assert final == hist[-1][1] == oracle.residual(oracle.mdf_step(u), u, "linf")
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "fp64"])
+def test_heat3d_fused_residual_in_kernel(dtype):
+    """3-D: the residual of every generation comes out of the sweep kernel itself (one launch, no second pass)."""
+    d, h, w, g = 37, 45, 150, 9
+    cfg = RunConfig(workload="heat3d", depth=d, height=h, width=w, backend="fused", dtype=dtype, residual="linf")
+    npdt = np.float32 if dtype == "fp32" else np.float64
+    with Solver(cfg) as s:
+        s.initialize()
+        st = s.run(g, residual=True)
+        assert st.launches == 1 and len(st.residual_history) == g
+        got = s.gather()
+        l2_last = float(np.sqrt(s._last_residual[0]))
+    u = oracle.heat3d_init(d, h, w, dtype=npdt)
+    exp = []
+    for _ in range(g):
+        v = oracle.heat3d_step(u)
+        exp.append(oracle.residual(v, u, "linf"))
+        prev, u = u, v
+    assert [r for _, r in st.residual_history] == exp
+    assert got.tobytes() == u.tobytes()
+    assert l2_last == pytest.approx(oracle.residual(u, prev, "l2"), rel=1e-6)
+    with Solver(cfg) as s:                      # "final": only the last generation carries it
+        s.initialize()
+        st = s.run(g, residual="final")
+        assert st.launches == 1 and [r for _, r in st.residual_history] == exp[-1:]
+
+
+def test_heat3d_run_to_tolerance_single_launch():
+    d, h, w, tol = 20, 24, 40, 0.5
+    cfg = RunConfig(workload="heat3d", depth=d, height=h, width=w, backend="fused", tol=tol, max_generations=3000)
+    with Solver(cfg) as s:
+        s.initialize()
+        st = s.run_to_tolerance()
+        s.check_status()
+        got = s.gather()
+    u = oracle.heat3d_init(d, h, w)
+    conv = None
+    for gen in range(1, 3001):
+        v = oracle.heat3d_step(u)
+        if oracle.residual(v, u, "linf") <= tol:
+            conv = gen
+        u = v
+        if conv is not None:
+            break
+    assert st.launches == 1 and st.stop_reason == "converged"
+    assert st.generations == conv + 1               # the run ends one generation after the one that converged
+    assert got.tobytes() == oracle.heat3d_run(oracle.heat3d_init(d, h, w), st.generations).tobytes()
