@@ -53,6 +53,7 @@ def parse_args(argv=None):
     p.add_argument("--chunk-rows", type=int, default=0, help="rows per tile of the schedule (0 = default)")
     p.add_argument("--sync-mode", type=int, default=None, help="1 = grid barrier between sweeps, 2 = dataflow flags")
     p.add_argument("--prefetch", type=int, default=None, help="0 = no next-tile TMA prefetch (A/B)")
+    p.add_argument("--cluster3d", action="store_true", help="--impl nccl --workload heat3d: the cluster/DSMEM kernel")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--halo-message", default="row", choices=["row", "element"])
     p.add_argument("--coarse-halo-flags", action="store_true", help="one arrival counter per neighbour instead of per-strip flags")
@@ -109,7 +110,7 @@ def main(argv=None) -> int:
                     backend=backend,
                     decomposition=args.decomposition, seed=0 if args.workload == "life" else None,
                     time_block=args.time_block, residual="linf", generations=gps, halo_message=args.halo_message,
-                    extra={"chunk_rows": args.chunk_rows, "sync_mode": args.sync_mode, "prefetch": args.prefetch,
+                    extra={"chunk_rows": args.chunk_rows, "sync_mode": args.sync_mode, "cluster3d": args.cluster3d, "prefetch": args.prefetch,
                            "coarse_halo_flags": args.coarse_halo_flags})
     K, W = args.steps, max(args.warmup, 0)
 

@@ -104,6 +104,14 @@ int mcp_step2d(int op, int dtype, const void* in_dev, void* out_dev, int64_t pit
 int mcp_step3d(int dtype, const void* in_dev, void* out_dev, int64_t pitch, int64_t plane_pitch, int planes_alloc,
                int rows_alloc, int z0, int y0, int d, int h, int w, int z_lo, int z_hi, int y_lo, int y_hi,
                double coeff, void* stream);
+/* Same contract, thread-block-cluster version: pairs of CTAs that own y-adjacent 32-row tiles form a (1,2,1) cluster,
+ * each TMA-loads its own rows plus its OUTER halo row and reads the inner halo row from its partner's shared memory
+ * (mapa + ld.shared::cluster), one barrier.cluster per plane.  Needs dense planes (plane_pitch = pitch * rows_alloc),
+ * pitch % 32 == 0, a 128-byte aligned input and one allocated layer around the updated box.  Measured against the
+ * fused kernel in profiles/r2/heat3d_cluster.md.  No counterpart in the reference (no shared memory there at all). */
+int mcp_step3d_cluster(int dtype, const void* in_dev, void* out_dev, int64_t pitch, int64_t plane_pitch,
+                       int planes_alloc, int rows_alloc, int z0, int y0, int d, int h, int w, int z_lo, int z_hi,
+                       int y_lo, int y_hi, double coeff, void* stream);
 
 /* ---- fused halo + stencil (+ residual) persistent kernel -------------------------------------------
  * One cooperative launch advances `generations` generations: TMA-fed shared-memory row ring per warp,

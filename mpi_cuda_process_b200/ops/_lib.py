@@ -91,6 +91,7 @@ def _declare_cuda(lib: C.CDLL) -> None:
     lib.mcp_init_shell3d.argtypes = [i, vp, i64, i64, i, i, i, i, i, i, i, dbl, dbl, vp]
     lib.mcp_step2d.argtypes = [i, i, vp, vp, i64, i, i, i, i, i, i, i, i, i, i, vp]
     lib.mcp_step3d.argtypes = [i, vp, vp, i64, i64, i, i, i, i, i, i, i, i, i, i, i, dbl, vp]
+    lib.mcp_step3d_cluster.argtypes = [i, vp, vp, i64, i64, i, i, i, i, i, i, i, i, i, i, i, dbl, vp]
     lib.mcp_fused2d_create.argtypes = [C.POINTER(FusedDesc), c_void_pp]
     lib.mcp_fused2d_run.argtypes = [vp, i, i, i, vp]
     lib.mcp_fused2d_run_to_tolerance.argtypes = [vp, i, i, i, dbl, C.POINTER(i), vp]

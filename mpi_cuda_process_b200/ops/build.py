@@ -31,6 +31,7 @@ CUDA_SOURCES = [
     "stencil_plain.cu",
     "stencil2d_fused.cu",
     "heat3d_fused.cu",
+    "heat3d_cluster.cu",
     "residual.cu",
     "residual_noalloc.cu",
     "gather_pack.cu",

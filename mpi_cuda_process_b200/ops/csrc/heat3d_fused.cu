@@ -33,7 +33,17 @@ constexpr int k3Threads = 256;                 // 8 warps x 4 rows
 constexpr int k3TileRows = 32;
 constexpr int k3BoxRows = k3TileRows + 2;
 constexpr int k3RowBytes = 512 + 32;           // 128 fp32 (64 fp64) cells + 16-byte halo on both sides
-constexpr int k3Slots = 4;
+#ifndef MCP_H3_SLOTS
+#define MCP_H3_SLOTS 4
+#endif
+#ifndef MCP_H3_PERIOD
+#define MCP_H3_PERIOD 1
+#endif
+// Plane ring and planes per __syncthreads (the ring is refilled k3Period slots at a time).  Measured on B200
+// (profiles/r2/heat3d_ring.md): 4 slots / 1 plane per barrier is the fastest; 6 slots halve or third the barriers but
+// the larger shared-memory footprint costs more than the barriers saved.
+constexpr int k3Slots = MCP_H3_SLOTS;
+constexpr int k3Period = MCP_H3_PERIOD;
 constexpr int k3BoxBytes = k3BoxRows * k3RowBytes;             // 18496 bytes delivered by one TMA box
 constexpr int k3SlotBytes = (k3BoxBytes + 127) / 128 * 128;   // ring slots stay 128-byte aligned for TMA
 constexpr int k3SmemBytes = k3Slots * k3SlotBytes + 64;
@@ -278,10 +288,9 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 ptx::tma_load_3d(smem + st * k3SlotBytes, tm_in, &bars[st], x0 - HALO, ylo - 1, pz);
             };
             const int n_planes = (zhi - zlo) + 2;  // planes zlo-1 .. zhi
-            if (tid == 0) {
-                const int npro = n_planes < k3Slots ? n_planes : k3Slots;
-                for (int i = 0; i < npro; ++i) issue(use + i, zlo - 1 + i);
-            }
+            int issued = n_planes < k3Slots ? n_planes : k3Slots;  // planes put in flight so far (tid 0 acts on it)
+            if (tid == 0)
+                for (int i = 0; i < issued; ++i) issue(use + i, zlo - 1 + i);
 
             // this thread: rows r0..r0+3 of the tile (box rows r0+1..r0+4), columns x0 + lane*VEC ..
             const int r0 = warp * 4;
@@ -390,8 +399,15 @@ heat3d_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 for (int i = 0; i < 4; ++i) U[i] = Cc[i + 1];
 #pragma unroll
                 for (int i = 0; i < 6; ++i) Cc[i] = Dn[i];
-                __syncthreads();  // slot of plane pz-1 (use + s) is free: nobody reads it any more
-                if (tid == 0 && s + k3Slots < n_planes) issue(use + s + k3Slots, zlo - 1 + s + k3Slots);
+                // Every k3Period planes: all warps are past plane pz in shared memory (it lives on in registers), so
+                // the ring may hold planes pz+1 .. pz+k3Slots; put the missing ones in flight.
+                if ((s % k3Period) == k3Period - 1 && s + 1 < zhi - zlo) {
+                    __syncthreads();
+                    const int upto = min(n_planes, s + 2 + k3Slots);
+                    if (tid == 0)
+                        for (int i = issued; i < upto; ++i) issue(use + i, zlo - 1 + i);
+                    issued = max(issued, upto);
+                }
             }
             };
             const bool lean = !f_zm && !f_zp && !f_ym && !f_yp && (p.z0 + zlo >= 1) && (p.z0 + zhi - 1 <= p.d - 2) &&

@@ -693,7 +693,8 @@ class Solver:
                                             self.store_shape[0], self.block.start[0] - G, cfg.height, cfg.width,
                                             G, G + self.own_shape[0], ylo, yhi, xlo, xhi, s), "mcp_step2d")
         else:
-            _lib.check(self._lib.mcp_step3d(_MCP_DTYPE[cfg.dtype], src.data_ptr(), dst.data_ptr(), self.pitch,
+            step3d = self._lib.mcp_step3d_cluster if cfg.extra.get("cluster3d") else self._lib.mcp_step3d
+            _lib.check(step3d(_MCP_DTYPE[cfg.dtype], src.data_ptr(), dst.data_ptr(), self.pitch,
                                             self.store_shape[1] * self.pitch, self.store_shape[0],
                                             self.store_shape[1], self.block.start[0] - G, self.block.start[1] - G,
                                             cfg.depth, cfg.height, cfg.width, G, G + self.own_shape[0], G,

@@ -410,3 +410,17 @@ def test_heat3d_run_to_tolerance_single_launch():
     assert st.launches == 1 and st.stop_reason == "converged"
     assert st.generations == conv + 1               # the run ends one generation after the one that converged
     assert got.tobytes() == oracle.heat3d_run(oracle.heat3d_init(d, h, w), st.generations).tobytes()
+
+
+@pytest.mark.parametrize("dtype,shape", [("fp32", (20, 24, 40)), ("fp32", (37, 77, 260)), ("fp64", (19, 100, 150)),
+                                         ("fp32", (40, 33, 129))])
+def test_heat3d_cluster_dsmem_kernel_bitwise(dtype, shape):
+    """Thread-block clusters: y-adjacent CTAs share the tile-boundary row through DSMEM (mcp_step3d_cluster)."""
+    d, h, w = shape
+    cfg = RunConfig(workload="heat3d", depth=d, height=h, width=w, backend="nccl", dtype=dtype, extra={"cluster3d": True})
+    with Solver(cfg) as s:
+        s.initialize()
+        s.run(5)
+        got = s.gather()
+    npdt = np.float32 if dtype == "fp32" else np.float64
+    assert got.tobytes() == oracle.heat3d_run(oracle.heat3d_init(d, h, w, dtype=npdt), 5).tobytes()
