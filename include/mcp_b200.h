@@ -152,7 +152,9 @@ typedef struct mcp_fused2d_desc {
      * sum's association order is the switch's, so use the P2P variant when bit-identical sums across ranks matter. */
     void* nvls_local;
     void* nvls_mc;
-    /* Optional per-strip halo flags (finer than the two arrival counters): a zeroed array of 2 x MCP_MAX_STRIPS
+    /* Per-strip halo flags (needed for the barrier-free schedule between ranks; without them a plan with neighbours
+     * keeps the device-side grid barrier between sweeps, because one arrival counter per neighbour cannot tell the
+     * sweeps of a neighbour apart once that neighbour overlaps them): a zeroed array of 2 x MCP_MAX_STRIPS
      * 64-bit words per rank ([0][s] written by rank-1, [1][s] by rank+1), and the addresses of the rows this rank
      * writes: rank-1's [1][*] and rank+1's [0][*].  A boundary tile then waits only for the neighbour's boundary
      * tiles of strips s-1, s, s+1 of the previous sweep. */

@@ -43,7 +43,9 @@ def read_ghw(stream=None, out=None) -> List[int]:
 
 def build_parser() -> argparse.ArgumentParser:
     p = argparse.ArgumentParser(prog="mpi_cuda_process_b200", description=__doc__.split("\n\n")[0])
-    p.add_argument("--workload", choices=["mdf", "life", "heat3d"], default="mdf")
+    from . import models
+    p.add_argument("--workload", choices=sorted(models.REGISTRY), default="mdf",
+                   help="; ".join(f"{w.name}: {w.description}" for w in models.REGISTRY.values()))
     p.add_argument("-g", "--generations", type=int, default=None)
     p.add_argument("--height", type=int, default=None)
     p.add_argument("--width", type=int, default=None)
@@ -71,6 +73,7 @@ def build_parser() -> argparse.ArgumentParser:
                    help="print the final life grid in the reference's print_array format")
     p.add_argument("--check", action="store_true", help="compare with the CPU oracle (small grids)")
     p.add_argument("--json", action="store_true", help="print run statistics as one JSON line")
+    p.add_argument("--log-jsonl", default=None, help="append run statistics as JSON lines to this file (rank 0)")
     p.add_argument("--no-prompt", action="store_true", help="do not read g/h/w from stdin (flags only)")
     p.add_argument("--checkpoint-dir", default=None)
     p.add_argument("--checkpoint-every", type=int, default=0)
@@ -155,6 +158,11 @@ def main(argv: Optional[List[str]] = None) -> int:
                 "glups": round(stats.glups, 3), "launches": stats.launches,
                 "residual": stats.residual_history[-1][1] if stats.residual_history else None,
             }
+            if args.log_jsonl:
+                from .utils.log import JsonlLogger
+                lg = JsonlLogger(args.log_jsonl, rank=ctx.rank)
+                lg.log(**summary, residual_history=stats.residual_history[-64:], stop_reason=stats.stop_reason)
+                lg.close()
             if args.json:
                 print(json.dumps(summary))
             else:

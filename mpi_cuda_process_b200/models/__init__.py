@@ -2,7 +2,8 @@
 
 The reference ships two programs that differ only in cell type and update rule (``diff kernel.cu
 MDF_kernel.cu``): the 2-D 5-point MDF heat/Jacobi update on floats and Conway's Game of Life on ints.
-Each workload here is described by a :class:`Workload` record (rule, dtypes, traffic model, oracle) and the
+Each workload here is described by a :class:`Workload` record (rule, dtypes, traffic model, oracle, operator code
+and time-block limits of the fused kernel, boundary rule); ``Solver`` and the CLI dispatch through the registry.  The
 3-D 7-point heat equation is added as the extension BASELINE.json names.
 """
 from __future__ import annotations
@@ -17,13 +18,26 @@ from .. import oracle
 class Workload:
     name: str
     ndim: int
-    dtypes: Tuple[str, ...]
+    dtypes: Tuple[str, ...]              # storage types ("bits" = bit-packed life cells)
     stencil_points: int
     flops_per_update: int
     reference: str                      # file:line of the rule in the reference
     init: Callable
     step: Callable
     description: str
+    op_code: int = -1                   # MCP_OP_* of the fused 2-D kernel (-1: not a 2-D operator)
+    max_time_block: Tuple[Tuple[str, int], ...] = ()   # (dtype, largest register-resident time block) pairs
+
+    def time_block_limit(self, dtype: str) -> int:
+        """Largest number of generations the fused kernel advances per pass over the field for this dtype."""
+        return dict(self.max_time_block).get(dtype, 1)
+
+    def evolving_box(self, cfg) -> Tuple[int, int, int, int]:
+        """Inclusive global box (ylo, yhi, xlo, xhi) of the cells that evolve; cells outside keep their value."""
+        h, w = cfg.height, cfg.width
+        if self.name == "life" and cfg.bc == "dead-outside":
+            return 0, h - 1, 0, w - 1
+        return 1, h - 2, 1, w - 2
 
     def bytes_per_update(self, dtype: str) -> int:
         """Compulsory HBM traffic of one update: one read + one write of the cell."""

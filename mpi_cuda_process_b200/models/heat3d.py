@@ -12,4 +12,5 @@ HEAT3D = Workload(
     reference="extension (no 3-D code in the reference)",
     init=oracle.heat3d_init, step=oracle.heat3d_step,
     description="3-D 7-point heat, Dirichlet shell",
+    max_time_block=(("fp32", 1), ("fp64", 1)),
 )

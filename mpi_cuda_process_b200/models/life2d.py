@@ -9,8 +9,10 @@ from .. import oracle
 from . import Workload
 
 LIFE2D = Workload(
-    name="life", ndim=2, dtypes=("int32",), stencil_points=9, flops_per_update=10,
+    name="life", ndim=2, dtypes=("int32", "bits"), stencil_points=9, flops_per_update=10,
     reference="kernel.cu:61,66",
     init=oracle.life_init_reference, step=oracle.life_step,
     description="Game of Life B3/S23, 8-neighbourhood",
+    # bit-packed cells: measured 24.4 TLUPS at TB=2 vs 16.3 at TB=4 (36 window registers per level)
+    op_code=1, max_time_block=(("int32", 4), ("bits", 2)),
 )

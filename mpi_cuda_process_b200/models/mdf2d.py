@@ -12,4 +12,5 @@ MDF2D = Workload(
     reference="MDF_kernel.cu:20",
     init=oracle.mdf_init, step=oracle.mdf_step,
     description="2-D 5-point heat/Jacobi, Dirichlet ring",
+    op_code=0, max_time_block=(("fp32", 8), ("fp64", 8)),
 )

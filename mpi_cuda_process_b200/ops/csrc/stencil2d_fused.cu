@@ -1131,6 +1131,11 @@ void account(mcp_fused2d_plan* pl, const LaunchSpec& ls, int executed, int warps
 int choose_mode(const mcp_fused2d_plan* pl, bool every_sweep_residual) {
     if (every_sweep_residual) return 0;  // CTA 0 reduces a finished sweep behind the grid barrier
     if (pl->sync_mode == 1) return 0;
+    // One arrival COUNTER per neighbour cannot tell sweeps apart once the neighbour runs barrier-free: its early
+    // strips of sweep k+1 would be counted for a late strip of sweep k (found by the injected-delay stress test).
+    // Without per-strip flags the ranks therefore keep the grid barrier, which orders a rank's sweeps.
+    const bool neighbours = pl->d.up_buf[0] != nullptr || pl->d.dn_buf[0] != nullptr;
+    if (neighbours && pl->d.strip_flags == nullptr) return 0;
     return 1;
 }
 

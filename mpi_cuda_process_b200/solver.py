@@ -25,7 +25,7 @@ from typing import List, Optional, Tuple
 import numpy as np
 import torch
 
-from . import oracle
+from . import models, oracle
 from .config import RunConfig
 from .parallel.context import DistContext, init_context
 from .parallel.decomp import Decomposition
@@ -34,7 +34,6 @@ from .parallel import host_p2p
 _TORCH_DTYPE = {"fp32": torch.float32, "fp64": torch.float64, "int32": torch.int32, "bits": torch.int32}
 _NP_DTYPE = {"fp32": np.float32, "fp64": np.float64, "int32": np.int32, "bits": np.int32}
 _MCP_DTYPE = {"fp32": 0, "fp64": 1, "int32": 2, "bits": 3}
-_MCP_OP = {"mdf": 0, "life": 1}
 
 
 @dataclass
@@ -81,6 +80,9 @@ class Solver:
         self._own_ctx = ctx is None
         self.ctx = ctx if ctx is not None else init_context(device="cpu" if cfg.backend == "cpu" else device)
         self.backend = self._pick_backend()
+        self.model = models.get(cfg.workload)    # rule, operator code, time-block limits, boundary rule
+        if cfg.dtype not in self.model.dtypes:
+            raise ValueError(f"workload {cfg.workload!r} stores {self.model.dtypes}, not {cfg.dtype!r}")
         self.bits = cfg.dtype == "bits"          # bit-packed life: 32 cells per stored 32-bit word
         if self.bits and self.backend != "fused":
             raise ValueError("dtype='bits' (bit-packed life) runs on the fused GPU backend only")
@@ -90,9 +92,7 @@ class Solver:
         self.esize = 8 if cfg.dtype == "fp64" else 4
         # ghost depth: the fused kernel exchanges `time_block` rows every `time_block` generations
         if self.backend == "fused" and self.ndim == 2:
-            tbmax = 8 if cfg.workload == "mdf" else 4
-            if self.bits:
-                tbmax = 2      # measured: 24.4 TLUPS at TB=2 vs 16.3 at TB=4 (36 window registers per level)
+            tbmax = self.model.time_block_limit(cfg.dtype)
             tb = 1
             while tb * 2 <= min(cfg.time_block, tbmax):
                 tb *= 2
@@ -135,10 +135,7 @@ class Solver:
     @property
     def _fix_bounds(self):
         """Inclusive global box of cells that evolve: (ylo, yhi, xlo, xhi)."""
-        h, w = self.cfg.height, self.cfg.width
-        if self.cfg.workload == "life" and self.cfg.bc == "dead-outside":
-            return 0, h - 1, 0, w - 1
-        return 1, h - 2, 1, w - 2
+        return self.model.evolving_box(self.cfg)
 
     def _alloc(self) -> None:
         cfg, G = self.cfg, self.ghost
@@ -252,7 +249,7 @@ class Solver:
         from .ops import _lib
         cfg, G = self.cfg, self.ghost
         d = _lib.FusedDesc()
-        d.op, d.dtype = _MCP_OP[cfg.workload], _MCP_DTYPE[cfg.dtype]
+        d.op, d.dtype = self.model.op_code, _MCP_DTYPE[cfg.dtype]
         d.h, d.w = cfg.height, cfg.width
         d.row_start, d.rows_own, d.ghost = self.block.start[0], self.own_shape[0], G
         d.pitch = self.pitch
@@ -688,7 +685,7 @@ class Solver:
         s = self._stream()
         if self.ndim == 2:
             ylo, yhi, xlo, xhi = self._fix_bounds
-            op = _MCP_OP[cfg.workload] | (0x100 if cfg.strict_fp64_accum and cfg.dtype == "fp32" else 0)
+            op = self.model.op_code | (0x100 if cfg.strict_fp64_accum and cfg.dtype == "fp32" else 0)
             _lib.check(self._lib.mcp_step2d(op, _MCP_DTYPE[cfg.dtype], src.data_ptr(), dst.data_ptr(), self.pitch,
                                             self.store_shape[0], self.block.start[0] - G, cfg.height, cfg.width,
                                             G, G + self.own_shape[0], ylo, yhi, xlo, xhi, s), "mcp_step2d")

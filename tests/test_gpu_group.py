@@ -119,3 +119,21 @@ def test_run_to_tolerance_refuses_a_local_stop_decision():
         assert rc == -2 and b"residual exchange" in emu.lib.mcp_last_error()
     finally:
         emu.close()
+
+
+def test_coarse_halo_counters_keep_the_grid_barrier():
+    """Found by scripts/stress_fused.py: with ONE arrival counter per neighbour (no per-strip flags) a barrier-free
+    neighbour's early strips of sweep k+1 were counted for a late strip of sweep k.  Such plans now keep the grid
+    barrier; this is the case that failed (3 ranks, injected delays, two launches, final residual on the first)."""
+    from _emu import EmulatedRanks
+    h, w, n, tb = 136, 1422, 3, 8
+    f0 = _field(h, w, seed=4)
+    emu = EmulatedRanks(f0, n, tb, strip_flags=False, chunk_rows=24,
+                        options={MCP_OPT_DEBUG_FLAGS: 8, MCP_OPT_SYNC_MODE: 2})
+    try:
+        emu.run(5 * tb, residual_mode=2)
+        emu.run(1 * tb)
+        assert emu.status() == [0] * n
+        assert emu.field().tobytes() == oracle.mdf_run(f0, 6 * tb).tobytes()
+    finally:
+        emu.close()

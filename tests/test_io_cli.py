@@ -76,3 +76,14 @@ def test_cli_life_print(tmp_path):
     ref = oracle.life_run(oracle.life_init_reference(12, 10), 3)
     assert out.read_bytes() == mio.format_array(ref)
     assert mio.format_array(ref).decode() in r.stdout
+
+
+def test_cli_logs_jsonl(tmp_path):
+    import json, subprocess, sys
+    log = tmp_path / "run.jsonl"
+    r = subprocess.run([sys.executable, "-m", "mpi_cuda_process_b200", "--workload", "mdf", "--backend", "cpu", "--no-prompt",
+                        "-g", "3", "--height", "12", "--width", "10", "--residual", "linf", "--log-jsonl", str(log)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    rec = json.loads(log.read_text().splitlines()[-1])
+    assert rec["workload"] == "mdf" and rec["generations"] == 3 and "ts" in rec

@@ -43,3 +43,15 @@ def test_workload_registry():
     import pytest
     with pytest.raises(ValueError):
         models.get("nope")
+
+
+def test_solver_dispatches_through_the_workload_registry():
+    from mpi_cuda_process_b200 import RunConfig, Solver
+    assert models.get("mdf").time_block_limit("fp32") == 8 and models.get("life").time_block_limit("bits") == 2
+    assert models.get("life").op_code == 1 and models.get("heat3d").op_code == -1
+    cfg = RunConfig(workload="life", height=9, width=7, backend="cpu", bc="dead-outside")
+    with Solver(cfg) as s:
+        assert s.model is models.get("life") and s._fix_bounds == (0, 8, 0, 6)
+    cfg = RunConfig(workload="mdf", height=9, width=7, backend="cpu")
+    with Solver(cfg) as s:
+        assert s._fix_bounds == (1, 7, 1, 5)
