@@ -16,14 +16,29 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
     return z ^ (z >> 31);
 }
 
+template <class B, int N>
+struct alignas(sizeof(B) * N) SumVec {
+    B v[N];
+};
+
 template <class B>  // B = unsigned (4-byte cells) or unsigned long long (fp64)
 __global__ void __launch_bounds__(256) checksum2d_kernel(const B* __restrict__ u, long long pitch, int w, int row_lo,
                                                          int nrows, long long grow0, unsigned long long* out) {
+    constexpr int VPT = 16 / (int)sizeof(B);
     unsigned long long acc = 0;
+    const bool vec = ((uintptr_t)u % 16 == 0) && (pitch % VPT == 0);
+    const int nvec = vec ? w / VPT : 0;
+    const int tx = blockIdx.x * blockDim.x + threadIdx.x, sx = gridDim.x * blockDim.x;
     for (int row = blockIdx.y; row < nrows; row += gridDim.y) {
         const B* s = u + (long long)(row_lo + row) * pitch;
         const unsigned long long base = (unsigned long long)(grow0 + row) * (unsigned long long)w;
-        for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < w; c += gridDim.x * blockDim.x)
+        for (int v = tx; v < nvec; v += sx) {
+            const SumVec<B, VPT> x = reinterpret_cast<const SumVec<B, VPT>*>(s)[v];  // one 16-byte load
+#pragma unroll
+            for (int k = 0; k < VPT; ++k)
+                acc += mix64((unsigned long long)x.v[k] ^ ((base + (unsigned)(v * VPT + k)) * 0x9e3779b97f4a7c15ull));
+        }
+        for (int c = nvec * VPT + tx; c < w; c += sx)
             acc += mix64((unsigned long long)s[c] ^ ((base + c) * 0x9e3779b97f4a7c15ull));
     }
 #pragma unroll
@@ -45,7 +60,7 @@ extern "C" int mcp_checksum2d(int dtype, const void* u_dev, int64_t pitch, int w
     MCP_CUDA_TRY(cudaMemsetAsync(out_dev, 0, 8, s));
     const int nrows = row_hi - row_lo;
     if (nrows == 0) return MCP_OK;
-    dim3 grid(std::max(1, std::min(8, (w + 255) / 256)), std::min(nrows, 148 * 4));
+    dim3 grid(std::max(1, std::min(4, (w / 4 + 255) / 256)), std::min(nrows, 148 * 8));
     if (dtype == MCP_DTYPE_F64)
         checksum2d_kernel<unsigned long long><<<grid, 256, 0, s>>>((const unsigned long long*)u_dev, pitch, w, row_lo,
                                                                    nrows, grow0, (unsigned long long*)out_dev);

@@ -11,18 +11,42 @@ namespace mcp {
 constexpr int kResBlocks = 592;  // 148 SMs x 4
 constexpr int kResThreads = 256;
 
+constexpr int kResGridX = 4;                       // blocks along a row
+constexpr int kResGridY = kResBlocks / kResGridX;  // blocks over the rows (grid-stride)
+
+template <class T, int N>
+struct alignas(sizeof(T) * N) ResVec {
+    T v[N];
+};
+
+// blockIdx.y walks the rows, threads walk a row in 16-byte vectors (scalar tail / fallback when w or the base
+// address does not allow it): no per-element divide, 16-byte loads.
 template <class T>
 __device__ __forceinline__ void block_partial(const T* __restrict__ a, const T* __restrict__ b, long long pitch,
                                               int w, int row_lo, int row_hi, double* part) {
+    constexpr int VPT = 16 / (int)sizeof(T);
     double ss = 0.0, mx = 0.0;
-    const long long ncell = (long long)(row_hi - row_lo) * w;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < ncell;
-         i += (long long)gridDim.x * blockDim.x) {
-        const int r = (int)(i / w), c = (int)(i - (long long)r * w);
-        const long long off = (long long)(row_lo + r) * pitch + c;
-        const double d = (double)(T)(a[off] - b[off]);  // difference in the field's own precision
-        ss = fma(d, d, ss);
-        mx = fmax(mx, fabs(d));
+    const bool vec = ((uintptr_t)a % 16 == 0) && ((uintptr_t)b % 16 == 0) && (pitch % VPT == 0);
+    const int nvec = vec ? w / VPT : 0;
+    const int tx = blockIdx.x * blockDim.x + threadIdx.x, sx = gridDim.x * blockDim.x;
+    for (int r = row_lo + blockIdx.y; r < row_hi; r += gridDim.y) {
+        const T* ra = a + (long long)r * pitch;
+        const T* rb = b + (long long)r * pitch;
+        for (int v = tx; v < nvec; v += sx) {
+            const ResVec<T, VPT> va = reinterpret_cast<const ResVec<T, VPT>*>(ra)[v];
+            const ResVec<T, VPT> vb = reinterpret_cast<const ResVec<T, VPT>*>(rb)[v];
+#pragma unroll
+            for (int k = 0; k < VPT; ++k) {
+                const double d = (double)(T)(va.v[k] - vb.v[k]);  // difference in the field's own precision
+                ss = fma(d, d, ss);
+                mx = fmax(mx, fabs(d));
+            }
+        }
+        for (int c = nvec * VPT + tx; c < w; c += sx) {
+            const double d = (double)(T)(ra[c] - rb[c]);
+            ss = fma(d, d, ss);
+            mx = fmax(mx, fabs(d));
+        }
     }
     __shared__ double s_ss[kResThreads / 32], s_mx[kResThreads / 32];
 #pragma unroll
@@ -41,8 +65,9 @@ __device__ __forceinline__ void block_partial(const T* __restrict__ a, const T* 
             a2 += s_ss[k];
             m2 = fmax(m2, s_mx[k]);
         }
-        part[2 * blockIdx.x] = a2;
-        part[2 * blockIdx.x + 1] = m2;
+        const int blk = blockIdx.y * gridDim.x + blockIdx.x;
+        part[2 * blk] = a2;
+        part[2 * blk + 1] = m2;
     }
 }
 
@@ -86,13 +111,13 @@ int mcp_residual2d(int dtype, const void* a, const void* b, int64_t pitch, int w
     cudaStream_t s = (cudaStream_t)stream;
     double* part = (double*)scratch;
     if (dtype == MCP_DTYPE_F32)
-        residual_pass1<float><<<kResBlocks, kResThreads, 0, s>>>((const float*)a, (const float*)b, pitch, w, row_lo,
+        residual_pass1<float><<<dim3(kResGridX, kResGridY), kResThreads, 0, s>>>((const float*)a, (const float*)b, pitch, w, row_lo,
                                                                  row_hi, part);
     else if (dtype == MCP_DTYPE_F64)
-        residual_pass1<double><<<kResBlocks, kResThreads, 0, s>>>((const double*)a, (const double*)b, pitch, w,
+        residual_pass1<double><<<dim3(kResGridX, kResGridY), kResThreads, 0, s>>>((const double*)a, (const double*)b, pitch, w,
                                                                   row_lo, row_hi, part);
     else if (dtype == MCP_DTYPE_I32)
-        residual_pass1<int><<<kResBlocks, kResThreads, 0, s>>>((const int*)a, (const int*)b, pitch, w, row_lo, row_hi,
+        residual_pass1<int><<<dim3(kResGridX, kResGridY), kResThreads, 0, s>>>((const int*)a, (const int*)b, pitch, w, row_lo, row_hi,
                                                                part);
     else
         MCP_REQUIRE(false, "mcp_residual2d: bad dtype %d", dtype);
