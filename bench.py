@@ -54,6 +54,7 @@ def parse_args(argv=None):
     p.add_argument("--sync-mode", type=int, default=None, help="1 = grid barrier between sweeps, 2 = dataflow flags")
     p.add_argument("--prefetch", type=int, default=None, help="0 = no next-tile TMA prefetch (A/B)")
     p.add_argument("--cluster3d", action="store_true", help="--impl nccl --workload heat3d: the cluster/DSMEM kernel")
+    p.add_argument("--e2e-depth", type=int, default=1, help="steps enqueued ahead of the result being read (e2e)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--halo-message", default="row", choices=["row", "element"])
     p.add_argument("--coarse-halo-flags", action="store_true", help="one arrival counter per neighbour instead of per-strip flags")
@@ -163,11 +164,17 @@ def main(argv=None) -> int:
             # ranks' launches are not separated by a host round trip per step (the copy itself happens every step).
             pending = []
 
+            marks = []                                    # (event before the step's device work, event after it)
+
             def one_step():
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
                 s.commit_input()                          # this step's input (uploaded while the previous step ran)
                 s.stage_input(host)                       # pinned host -> device for the next step, overlapped
                 pending.append(s.run_async(gps))          # solve + async 32-byte result copy
-                return pending.pop(0).wait() if len(pending) > 1 else None
+                e1.record()
+                marks.append((e0, e1))
+                return pending.pop(0).wait() if len(pending) > args.e2e_depth else None
 
             def drain():
                 r = None
@@ -183,6 +190,7 @@ def main(argv=None) -> int:
             ctx.barrier()
             t0 = time.perf_counter()
             last = None
+            del marks[:]
             l0 = s.total_stats.launches
             for _ in range(K):
                 r = one_step()
@@ -191,6 +199,11 @@ def main(argv=None) -> int:
             torch.cuda.synchronize()                      # includes the upload issued in the last step
             t1 = time.perf_counter()
             e2e_ms = ctx.all_reduce_max((t1 - t0) * 1e3)
+            # device timeline of the steps: time inside a step's device work and idle gaps between consecutive steps
+            busy = [a.elapsed_time(b) for a, b in marks]
+            gaps = [marks[i][1].elapsed_time(marks[i + 1][0]) for i in range(len(marks) - 1)]
+            step_busy_ms = ctx.all_reduce_max(sum(busy) / max(len(busy), 1))
+            step_gap_ms = ctx.all_reduce_max(sum(gaps) / max(len(gaps), 1)) if gaps else 0.0
             # what bounds a step: the solve, or the host -> device upload of its input?  (device-timed, max over ranks;
             # "overlapped" = while the solve of the previous step runs, "alone" = all ranks uploading, GPUs idle)
             h2d_overlapped_ms = ctx.all_reduce_max(s.last_upload_ms() or 0.0)
@@ -204,7 +217,9 @@ def main(argv=None) -> int:
                    "launches_per_step": (s.total_stats.launches - l0) / max(K, 1),
                    "h2d_ms_overlapped_max": round(h2d_overlapped_ms, 3), "h2d_ms_alone_max": round(h2d_alone_ms, 3),
                    "h2d_gbs_per_gpu_overlapped": round(h2d / (h2d_overlapped_ms * 1e-3) / 1e9, 2) if h2d_overlapped_ms > 0 else None,
-                   "bound": "upload" if h2d_overlapped_ms > 0.9 * e2e_ms / K else "solve"}
+                   "bound": "upload" if h2d_overlapped_ms > 0.9 * e2e_ms / K else "solve",
+                   "device_ms_per_step_busy_max": round(step_busy_ms, 3),
+                   "device_ms_idle_between_steps_max": round(step_gap_ms, 3), "pipeline_depth": args.e2e_depth}
 
             # ---- the same, with the solution field gathered to rank 0 and copied to the host every step ----
             Kg = max(1, min(K, 4))
