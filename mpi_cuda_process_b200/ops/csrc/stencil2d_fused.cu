@@ -40,8 +40,14 @@ namespace mcp {
 
 constexpr int kWarpsPerCta = 16;
 constexpr int kThreads = kWarpsPerCta * 32;
-constexpr int kRowsPerStage = 6;  // multiple of 3: the 3-row register window rotates at compile time
-constexpr int kStages = 4;
+#ifndef MCP_ROWS_PER_STAGE
+#define MCP_ROWS_PER_STAGE 6
+#endif
+#ifndef MCP_STAGES
+#define MCP_STAGES 4
+#endif
+constexpr int kRowsPerStage = MCP_ROWS_PER_STAGE;  // multiple of 3: the 3-row register window rotates at compile time
+constexpr int kStages = MCP_STAGES;
 constexpr int kRowBytes = 512;  // 32 lanes x 16 B
 constexpr int kStageBytes = kRowsPerStage * kRowBytes;
 constexpr int smem_bytes_for(int warps) { return warps * kStages * kStageBytes + warps * kStages * 8; }
@@ -1000,7 +1006,13 @@ int pick_tb(int tb, bool res, bool group, const void** fn, int* warps) {
     return MCP_ERR_UNSUPPORTED;
 }
 
-int pick_kernel(const mcp_fused2d_desc& d, int tb, bool res, bool group, const void** fn, int* warps) {
+int pick_kernel(const mcp_fused2d_desc& d, int tb, bool res, bool group, const void** fn, int* warps,
+                bool scalar = false) {
+    if (scalar && !group && d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F32 && tb == 8) {
+        *fn = kernel_ptr<MdfF32Scalar, 8>(res, false);
+        *warps = kernel_warps<MdfF32Scalar, 8>();
+        return MCP_OK;
+    }
     if (d.op == MCP_OP_MDF && d.dtype == MCP_DTYPE_F32) {
         if (tb == 8) { *fn = kernel_ptr<MdfF32, 8>(res, group); *warps = kernel_warps<MdfF32, 8>(); return MCP_OK; }
         return pick_tb<MdfF32>(tb, res, group, fn, warps);
@@ -1019,6 +1031,7 @@ int pick_kernel(const mcp_fused2d_desc& d, int tb, bool res, bool group, const v
 struct LaunchSpec {
     int tb, sweeps, mode;  // mode: 0 = grid barrier, 1 = dataflow
     bool res;              // residual instantiation of the kernel
+    bool scalar = false;   // fp32 MDF, TB = 8: scalar operator (see prefers_scalar_barrier)
     int res_first_sweep;
     int stop_mode;
     double stop_thresh;
@@ -1128,9 +1141,21 @@ void account(mcp_fused2d_plan* pl, const LaunchSpec& ls, int executed, int warps
     pl->last_generations += executed * ls.tb;
 }
 
-int choose_mode(const mcp_fused2d_plan* pl, bool every_sweep_residual) {
+// fp32 MDF at TB = 8 on a slab with many tiles per warp: the scalar operator behind the grid barrier is the fastest
+// combination measured (16384^2 on one GPU, same box: scalar + barrier 3282, packed + barrier 3105, packed + dataflow
+// 3081, scalar + dataflow 3034 GLUPS); on small slabs packed + dataflow wins by far (2048 rows: 2740 vs 1880 / 2130).
+bool prefers_scalar_barrier(const mcp_fused2d_plan* pl, int tb) {
+    const mcp_fused2d_desc& d = pl->d;
+    if (pl->sync_mode != 0 || d.op != MCP_OP_MDF || d.dtype != MCP_DTYPE_F32 || tb != 8) return false;
+    const Geometry& g = pl->geo[tb_index(tb)][0];
+    const double tiles_per_warp = (double)g.n_strips * g.n_chunks() / ((double)pl->grid * warps_for(0, tb));
+    return tiles_per_warp >= 5.0;
+}
+
+int choose_mode(const mcp_fused2d_plan* pl, int tb, bool every_sweep_residual) {
     if (every_sweep_residual) return 0;  // CTA 0 reduces a finished sweep behind the grid barrier
     if (pl->sync_mode == 1) return 0;
+    if (prefers_scalar_barrier(pl, tb)) return 0;
     // One arrival COUNTER per neighbour cannot tell sweeps apart once the neighbour runs barrier-free: its early
     // strips of sweep k+1 would be counted for a late strip of sweep k (found by the injected-delay stress test).
     // Without per-strip flags the ranks therefore keep the grid barrier, which orders a rank's sweeps.
@@ -1262,7 +1287,7 @@ int mcp_fused2d_set_option(mcp_fused2d_plan* pl, int option, long long value) {
 int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_strips, int* n_chunks, int* grid,
                          int* smem_bytes) {
     MCP_REQUIRE(pl, "null plan");
-    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     if (n_strips) *n_strips = g.n_strips;
     if (n_chunks) *n_chunks = g.n_chunks();
     if (grid) *grid = pl->grid;
@@ -1273,7 +1298,7 @@ int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_stri
 // Heights of the row chunks (= tiles) of the default schedule, in slab order.
 int mcp_fused2d_chunks(const mcp_fused2d_plan* pl, int time_block, int* rows_out, int max_entries) {
     MCP_REQUIRE(pl && rows_out, "null argument");
-    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     const int n = std::min(g.n_chunks(), max_entries);
     for (int i = 0; i < n; ++i) rows_out[i] = g.chunk_y[i + 1] - g.chunk_y[i];
     return n;
@@ -1285,7 +1310,7 @@ static int launch(mcp_fused2d_plan* pl, const LaunchSpec& ls, cudaStream_t strea
     if (rc) return rc;
     const void* fn = nullptr;
     int warps = 0;
-    rc = pick_kernel(pl->d, ls.tb, ls.res, false, &fn, &warps);
+    rc = pick_kernel(pl->d, ls.tb, ls.res, false, &fn, &warps, ls.scalar);
     if (rc) return rc;
     if (ls.stop_mode != 0) MCP_CUDA_TRY(cudaMemsetAsync(&pl->result->stop_word, 0, 2 * sizeof(int), stream));
     if (ls.mode == 1)
@@ -1324,8 +1349,9 @@ static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, int r
         if (stop_mode != 0) ls.sweeps = std::min(ls.sweeps, kMaxResSlots);
         ls.stop_mode = stop_mode;
         ls.stop_thresh = stop_thresh;
-        ls.mode = choose_mode(pl, ls.res && ls.res_first_sweep < ls.sweeps - 1);
+        ls.mode = choose_mode(pl, tb, ls.res && ls.res_first_sweep < ls.sweeps - 1);
         if (stop_mode != 0) ls.mode = 0;
+        ls.scalar = ls.mode == 0 && prefers_scalar_barrier(pl, tb);
 
         int warps = 0;
         int rc = launch(pl, ls, stream, &warps);
@@ -1409,7 +1435,11 @@ int mcp_fused2d_run_group(mcp_fused2d_plan** plans, int n, int generations, int 
     ls.res_first_sweep = residual_mode == MCP_RES_FINAL ? ls.sweeps - 1 : 0;
     ls.stop_mode = 0;
     ls.stop_thresh = 0.0;
-    ls.mode = choose_mode(p0, ls.res && ls.res_first_sweep < ls.sweeps - 1);
+    // same rules as choose_mode, minus the scalar-operator preference (the group kernel is built for the packed one)
+    const bool every = ls.res && ls.res_first_sweep < ls.sweeps - 1;
+    const bool coarse = p0->d.strip_flags == nullptr && (p0->d.up_buf[0] != nullptr || p0->d.dn_buf[0] != nullptr);
+    ls.mode = (every || coarse || p0->sync_mode == 1) ? 0 : 1;
+    ls.scalar = false;
     const void* fn = nullptr;
     int warps = 0;
     int rc = pick_kernel(p0->d, tb, ls.res, true, &fn, &warps);
@@ -1490,7 +1520,7 @@ int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost,
 // that a host tool can see which tiles are the critical path and where ranks wait for each other.
 int mcp_fused2d_tile_trace2(mcp_fused2d_plan* pl, int time_block, int which, uint32_t* ns_out, int max_entries) {
     MCP_REQUIRE(pl && ns_out && which >= 0 && which <= 2, "bad argument");
-    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     const int n = std::min(std::min(g.n_strips * g.n_chunks(), pl->last_tiles), max_entries);
     if (n > 0)
         MCP_CUDA_TRY(cudaMemcpy(ns_out, pl->tile_ns + (size_t)which * pl->partials_cap_tiles, (size_t)n * sizeof(uint32_t),
@@ -1501,7 +1531,7 @@ int mcp_fused2d_tile_trace2(mcp_fused2d_plan* pl, int time_block, int which, uin
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* pl, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
                            int max_entries) {
     MCP_REQUIRE(pl && ns_out, "null argument");
-    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, false)];
+    const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     const int nstr = g.n_strips, ng = g.n_chunks();
     const int n = std::min(std::min(nstr * ng, pl->last_tiles), max_entries);
     if (n > 0) MCP_CUDA_TRY(cudaMemcpy(ns_out, pl->tile_ns, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
