@@ -1147,6 +1147,7 @@ void account(mcp_fused2d_plan* pl, const LaunchSpec& ls, int executed, int warps
 bool prefers_scalar_barrier(const mcp_fused2d_plan* pl, int tb) {
     const mcp_fused2d_desc& d = pl->d;
     if (pl->sync_mode != 0 || d.op != MCP_OP_MDF || d.dtype != MCP_DTYPE_F32 || tb != 8) return false;
+    if (d.up_buf[0] != nullptr || d.dn_buf[0] != nullptr) return false;  // measured on single-GPU slabs only
     const Geometry& g = pl->geo[tb_index(tb)][0];
     const double tiles_per_warp = (double)g.n_strips * g.n_chunks() / ((double)pl->grid * warps_for(0, tb));
     return tiles_per_warp >= 5.0;

@@ -137,3 +137,28 @@ def test_tile_order_is_a_bijection_and_runs_outside_in(ns, nc):
     assert pos_of_chunk[0] == 0 and (nc == 1 or pos_of_chunk[nc - 1] == 1)
     for c in range(nc - 1):
         assert abs(pos_of_chunk[c] - pos_of_chunk[c + 1]) <= 2
+
+
+@settings(max_examples=60, deadline=None)
+@given(rows=st.integers(8, 40000), w=st.integers(64, 40000), tb=st.sampled_from([1, 2, 4, 8]), grid=st.sampled_from([18, 148]))
+def test_dataflow_schedule_invariants_without_a_gpu(rows, w, tb, grid):
+    """Barrier-free schedule (mode 1): constant chunk height with r + 2*TB a whole number of 6-row TMA stages, the last
+    chunk between half and 1.5x of it, and -- when the slab allows it -- at least two tiles per warp and sweep."""
+    import ctypes as C
+    from mpi_cuda_process_b200.ops import _lib
+    lib = _lib.cuda_lib()
+    ghost = tb
+    rows = max(rows, ghost)
+    out = (C.c_int * 8192)()
+    ns = C.c_int(0)
+    n = lib.mcp_fused2d_plan_schedule2(0, 0, w, rows, ghost, tb, grid, 0, 1, out, 8192, C.byref(ns))
+    assert 1 <= n <= 4096
+    hts = [out[i] for i in range(n)]
+    assert sum(hts) == rows and min(hts) >= min(ghost, rows)
+    if n > 1:
+        r = hts[0]
+        assert all(x == r for x in hts[:-1]) and (r + 2 * tb) % 6 == 0
+        assert r // 2 <= hts[-1] < 2 * r
+        warps = grid * (8 if tb == 8 else 16)
+        if r > max(ghost, 4 * tb) + 6:          # not already at the minimum tile height
+            assert n * ns.value >= 2 * warps * 0.9
