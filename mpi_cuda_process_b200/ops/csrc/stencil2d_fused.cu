@@ -6,7 +6,7 @@
 // run_mdf/middle_kernel/border_kernel (MDF_kernel.cu:10-70), game_of_life (kernel.cu:10-113).
 //
 // Design (B200-first, not a translation):
-//  * One cooperative launch runs many generations.  148 CTAs x 16 warps stay resident.
+//  * One cooperative launch runs many generations.  148 CTAs x 8..16 warps stay resident.
 //  * The slab is cut into tiles = (column strip of 32 lanes x 16 B) x (row chunk).  A tile belongs to ONE
 //    warp; warps never synchronise with each other inside a sweep.
 //  * Each warp owns a 4-stage shared-memory ring fed by TMA (cp.async.bulk.tensor.2d, 6 rows x 512 B
@@ -14,17 +14,19 @@
 //  * Temporal blocking in registers: a warp streams down the rows and carries TB generations as a
 //    wavefront (3-row window per level, compile-time rotated), so HBM sees one read + one write per
 //    TB generations.  Left/right neighbours come from warp shuffles.  Each update is the reference's
-//    exact rounding sequence, so results are bit-identical to a generation-at-a-time Jacobi.
+//    exact rounding sequence (fp32: on the packed fp32 pipe, FADD2 / FFMA2), so results are bit-identical to
+//    a generation-at-a-time Jacobi.
 //  * Tiles on the slab cut store their top/bottom `ghost` output rows twice: locally and straight into
-//    the neighbour GPU's ghost rows through an NVLink-mapped peer pointer, then bump a system-scope
-//    release counter in the neighbour's flag pad.  Tiles that read ghost rows acquire-spin on their local
-//    counter first.  Boundary tiles are scheduled first so the transfer overlaps the interior tiles.
-//  * Sweeps are separated by a device-side grid barrier (no host round trip, no NCCL, no MPI).
-//  * Optional fused residual: per-tile (sum d^2, max |d|) in fp64 -> fixed-order reduction (deterministic).
-#include <cooperative_groups.h>
-
-#include <stdlib.h>
-
+//    the neighbour GPU's ghost rows through an NVLink-mapped peer pointer, then ONE system-scope fence and
+//    relaxed signal writes into the neighbour's flag pad (per-strip sequence flags + an arrival counter).
+//    Tiles that read ghost rows acquire-spin (bounded) on their local flags first.  Boundary tiles are
+//    scheduled first so the transfer overlaps the interior tiles.
+//  * Between sweeps: per-tile dataflow flags (a tile of sweep k+1 waits for its nine neighbours of sweep k;
+//    one ticket stream over all sweeps; the next tile's first TMA stages are put in flight from the current
+//    tile's tail), or a device-side grid barrier where a finished sweep must be reduced.  No host round
+//    trip, no NCCL, no MPI.  Before a launch ends it drains the halo pushes addressed to this rank.
+//  * Optional fused residual: per-tile (sum d^2, max |d|) in fp64 -> fixed-order reduction by one warp ->
+//    all-reduce over the peers' inboxes (or NVLS multimem) -> history, stop decision, 32-byte result block.
 #include <algorithm>
 #include <type_traits>
 #include <cmath>
@@ -39,7 +41,6 @@
 namespace mcp {
 
 constexpr int kWarpsPerCta = 16;
-constexpr int kThreads = kWarpsPerCta * 32;
 #ifndef MCP_ROWS_PER_STAGE
 #define MCP_ROWS_PER_STAGE 6
 #endif
@@ -51,8 +52,8 @@ constexpr int kStages = MCP_STAGES;
 constexpr int kRowBytes = 512;  // 32 lanes x 16 B
 constexpr int kStageBytes = kRowsPerStage * kRowBytes;
 constexpr int smem_bytes_for(int warps) { return warps * kStages * kStageBytes + warps * kStages * 8; }
-constexpr int kSmemBytes = smem_bytes_for(kWarpsPerCta);
-// TB = 8 keeps 96 registers of row windows per thread: run 12 warps x 168 registers instead of 16 x 128.
+// TB = 8 keeps 96 registers of row windows per thread: 8 warps x up to 255 registers instead of 16 x 128 (12 warps x
+// 168 registers were measured too: no gain, profiles/README.md).
 constexpr int kWarpsTb8 = 8;
 #ifndef MCP_WARPS_F32_TB8
 #define MCP_WARPS_F32_TB8 8
