@@ -18,6 +18,7 @@ os.makedirs(OUT, exist_ok=True)
 KERNELS = [  # (object, mangled-name regex, file stem)
     ("stencil2d_fused.cu.o", r"fused2d_kernelINS_12MdfF32PackedELi8ELb0ELi8", "fused2d_mdf_f32_tb8"),
     ("stencil2d_fused.cu.o", r"fused2d_kernelINS_12MdfF32PackedELi8ELb1ELi8", "fused2d_mdf_f32_tb8_residual"),
+    ("stencil2d_fused.cu.o", r"fused2d_kernelINS_12MdfF32ScalarELi8ELb0ELi8", "fused2d_mdf_f32_scalar_tb8"),
     ("stencil2d_fused.cu.o", r"fused2d_kernelINS_6MdfF64ELi4ELb1ELi16", "fused2d_mdf_f64_tb4_residual"),
     ("stencil2d_fused.cu.o", r"fused2d_kernelINS_6LifeB1ELi2ELb0ELi12", "fused2d_life_bits_tb2"),
     ("stencil2d_fused.cu.o", r"fused2d_group_kernelINS_12MdfF32PackedELi8ELb0", "fused2d_group_mdf_f32_tb8"),
