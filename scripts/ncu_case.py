@@ -20,8 +20,10 @@ ap.add_argument("--generations", type=int, default=16)
 ap.add_argument("--chunk-rows", type=int, default=0)
 ap.add_argument("--dtype", default="fp32")
 ap.add_argument("--residual", action="store_true")
+ap.add_argument("--cluster3d", action="store_true", help="heat3d through the plain backend's cluster + DSMEM kernel")
 a = ap.parse_args()
-kw = dict(backend="fused", time_block=a.time_block, extra={"chunk_rows": a.chunk_rows})
+kw = dict(backend="nccl" if a.cluster3d else "fused", time_block=a.time_block,
+          extra={"chunk_rows": a.chunk_rows, "cluster3d": a.cluster3d})
 if a.what == "heat3d":
     cfg = RunConfig(workload="heat3d", depth=a.depth, height=a.height, width=a.width, dtype=a.dtype, **kw)
 elif a.what == "life":
