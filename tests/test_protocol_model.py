@@ -1,0 +1,84 @@
+"""Protocol checker: the flag rules of the fused 2-D kernel restated on an abstract machine and run under an
+adversarial scheduler (mpi_cuda_process_b200/utils/protocol_model.py).  CPU only.
+
+The reference has nothing to compare with: blocking MPI calls and cudaDeviceSynchronize are its whole protocol
+(MDF_kernel.cu:166-183).  What is pinned here is (a) the two combinations the kernel uses never read a stale or an
+overwritten region whatever the interleaving, and (b) the combination the kernel refuses -- one arrival counter per
+neighbour without a grid barrier -- is refused for a reason the model can show.
+"""
+import itertools
+
+import pytest
+
+from mpi_cuda_process_b200.utils.protocol_model import Model, ProtocolViolation, explore
+
+
+@pytest.mark.parametrize("flags,sync", [("strip", "dataflow"), ("strip", "barrier"), ("coarse", "barrier")])
+def test_sound_combinations_never_violate(flags, sync):
+    r = explore(seeds=120, ranks=3, chunks=3, strips=4, sweeps=5, warps=3, flags=flags, sync=sync)
+    assert r["violations"] == 0, r.get("first")
+    assert r["ok"] == 120
+
+
+def test_small_and_degenerate_geometries():
+    # one chunk (a tile that is both the upper and the lower edge), one strip, one warp, one rank
+    for R, C, S, W in itertools.product((1, 2, 4), (1, 2, 4), (1, 3), (1, 4)):
+        for flags, sync in (("strip", "dataflow"), ("coarse", "barrier")):
+            r = explore(seeds=8, ranks=R, chunks=C, strips=S, sweeps=4, warps=W, flags=flags, sync=sync)
+            assert r["violations"] == 0, (R, C, S, W, flags, sync, r.get("first"))
+
+
+def test_coarse_counter_without_barrier_is_unsound():
+    """The case the injected-delay stress run caught on the GPU: the kernel now forces such plans to barrier mode
+    (stencil2d_fused.cu choose_mode); the model shows why."""
+    r = explore(seeds=200, ranks=3, chunks=3, strips=4, sweeps=5, warps=3, flags="coarse", sync="dataflow")
+    assert r["violations"] > 0
+    assert "ghost" in r["first"] and "stale" in r["first"]
+
+
+def test_single_rank_coarse_dataflow_is_fine():
+    # no neighbours -> no counters involved: the barrier-free schedule alone is sound
+    r = explore(seeds=60, ranks=1, chunks=4, strips=4, sweeps=5, warps=4, flags="coarse", sync="dataflow")
+    assert r["violations"] == 0, r.get("first")
+
+
+def test_violation_is_reproducible_from_its_seed():
+    r = explore(seeds=200, ranks=3, chunks=3, strips=4, sweeps=5, warps=3, flags="coarse", sync="dataflow")
+    seed = int(r["first"].rsplit("seed=", 1)[1])
+    with pytest.raises(ProtocolViolation) as e1:
+        Model(ranks=3, chunks=3, strips=4, sweeps=5, warps=3, flags="coarse", sync="dataflow", seed=seed).run()
+    assert str(e1.value) == r["first"]
+
+
+def test_without_long_stalls_the_bug_hides():
+    """Documents why the stress test injects long delays: with only fine-grained interleaving a neighbour's sweeps
+    never separate and the unsound combination passes -- short random schedules are not evidence."""
+    r = explore(seeds=60, ranks=3, chunks=3, strips=4, sweeps=5, warps=3, flags="coarse", sync="dataflow",
+                stall_rate=0.0)
+    assert r["ok"] + r["violations"] == 60
+    assert r["violations"] <= 2
+
+
+MULTI = dict(ranks=3, chunks=3, strips=4, sweeps=3, warps=3, launches=3)
+
+
+@pytest.mark.parametrize("flags,sync", [("strip", "dataflow"), ("coarse", "barrier")])
+def test_back_to_back_launches_with_host_uploads_need_no_host_barrier(flags, sync):
+    """Solver.load_local / commit_input overwrite the slab between launches with no barrier between the ranks
+    (solver.py); drain_incoming at the end of every launch is what makes that safe."""
+    r = explore(seeds=100, flags=flags, sync=sync, **MULTI)
+    assert r["violations"] == 0, r.get("first")
+
+
+@pytest.mark.parametrize("flags,sync", [("strip", "dataflow"), ("coarse", "barrier")])
+def test_without_the_drain_an_upload_races_with_late_halo_pushes(flags, sync):
+    r = explore(seeds=60, flags=flags, sync=sync, drain=False, **MULTI)
+    assert r["violations"] > 0
+    assert "ghost" in r["first"]
+
+
+@pytest.mark.parametrize("flags,sync", [("strip", "dataflow"), ("coarse", "barrier")])
+def test_the_drain_is_only_needed_for_uploads(flags, sync):
+    # launches that continue from the previous state are ordered by the sequence flags alone
+    r = explore(seeds=100, flags=flags, sync=sync, drain=False, upload=False, **MULTI)
+    assert r["violations"] == 0, r.get("first")
