@@ -5,6 +5,7 @@ signalling, multimem or packed-fp32 instruction.  Runs on the build box (no GPU 
     python scripts/dump_sass.py
 """
 import gzip
+import io
 import os
 import re
 import subprocess
@@ -54,7 +55,9 @@ for obj, pat, stem in KERNELS:
         print("not found:", pat, file=sys.stderr)
         continue
     body = fns[name]
-    with gzip.open(os.path.join(OUT, stem + ".sass.gz"), "wt") as f:
+    with open(os.path.join(OUT, stem + ".sass.gz"), "wb") as raw, \
+            gzip.GzipFile(filename="", fileobj=raw, mode="wb", mtime=0) as gz, \
+            io.TextIOWrapper(gz) as f:          # mtime=0: identical input -> identical file
         f.write("Function : " + body)
     ins = [l for l in body.split("\n") if re.match(r"\s+/\*[0-9a-f]{4,6}\*/", l)]
     keys = [re.sub(r"\s+/\* 0x[0-9a-f]+ \*/\s*$", "", l).rstrip() for l in ins if KEY.search(l)]
@@ -81,5 +84,36 @@ for obj, pat, stem in KERNELS:
             open(os.path.join(OUT, stem + ".rowloop.sass"), "w").write(
                 f"// lean row loop of {name}: {len(best)} instructions for 6 rows x 8 levels x 4 cells per lane = 192 "
                 f"cell updates per lane ({len(best) / 192:.2f} instructions per update)\n" + "\n".join(clean) + "\n")
+
+
+def resource_usage():
+    """Registers / stack / static shared / local (spill) bytes of every kernel in the built library."""
+    lib = os.path.join(ROOT, "mpi_cuda_process_b200", "ops", "_lib", "libmcp_b200.so")
+    out = subprocess.run(["cuobjdump", "--dump-resource-usage", lib], capture_output=True, text=True).stdout.splitlines()
+    rows = []
+    for i, l in enumerate(out):
+        m = re.match(r"\s*Function (\S+):", l)
+        if not m:
+            continue
+        name = subprocess.run(["cu++filt", m.group(1)], capture_output=True, text=True).stdout.strip()
+        get = lambda k: int((re.search(k + r":(\d+)", out[i + 1]) or [None, "0"])[1])
+        rows.append((name, get("REG"), get("STACK"), get("SHARED"), get("LOCAL"), get(r"CONSTANT\[0\]")))
+    rows.sort()
+    with open(os.path.join(OUT, "resource_usage.txt"), "w") as f:
+        f.write("# cuobjdump --dump-resource-usage of libmcp_b200.so (sm_100a, -lineinfo).  STACK > 0 with LOCAL = 0 is "
+                "call frames\n# of the __noinline__ wait helpers, not spills; dynamic shared memory (TMA rings) is set at "
+                "launch and not listed.\n")
+        f.write(f"{'REG':>4} {'STACK':>6} {'SMEM':>6} {'LOCAL':>6} {'CONST0':>7}  kernel\n")
+        for n, r, st, sh, lo, c in rows:
+            f.write(f"{r:>4} {st:>6} {sh:>6} {lo:>6} {c:>7}  {n}\n")
+    return rows
+
+
+rows = resource_usage()
+index.append("")
+index.append(f"`resource_usage.txt`: registers, stack, static shared and local memory of all {len(rows)} kernels in the "
+             f"library (`cuobjdump --dump-resource-usage`): local memory (spills) is "
+             f"{max(r[4] for r in rows)} bytes everywhere; the widest sweep kernels use up to "
+             f"{max(r[1] for r in rows)} registers at 8 warps per CTA.")
 open(os.path.join(OUT, "README.md"), "w").write("\n".join(index) + "\n")
 print("\n".join(index[4:]))
