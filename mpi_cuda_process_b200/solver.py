@@ -72,6 +72,26 @@ class PendingResult:
         return self._value
 
 
+class _ResultRing:
+    """Bookkeeping of the pinned result slots: a fixed ring, so a slot may still belong to a handle nobody has waited
+    for when its turn comes again -- that handle is settled (its value read out) before the slot is handed on."""
+
+    def __init__(self, slots: int):
+        self.slots, self.next, self.owner = slots, 0, {}
+
+    def claim(self) -> int:
+        idx = self.next % self.slots
+        self.next += 1
+        older = self.owner.pop(idx, None)
+        if older is not None:
+            older.wait()
+        return idx
+
+    def bind(self, idx: int, handle):
+        self.owner[idx] = handle
+        return handle
+
+
 class Solver:
     """Distributed stencil solver.  Use as a context manager or call :meth:`close`."""
 
@@ -239,7 +259,6 @@ class Solver:
         if cfg.extra.get("timeout_ms") is not None:
             _lib.check(self._lib.mcp_fused3d_set_timeout_ms(plan, int(cfg.extra["timeout_ms"])))
         self._result_pool = torch.zeros((8, 4), dtype=torch.float64).pin_memory()
-        self._result_next = 0
 
     def _ensure_plan(self):
         if self._plan is not None:
@@ -304,7 +323,6 @@ class Solver:
                 _lib.check(self._lib.mcp_fused2d_set_option(plan, opt, int(cfg.extra[key])), "mcp_fused2d_set_option")
         # one pinned 32-byte block for (status, stop word, sweeps done, last residual): read back with one async copy
         self._result_pool = torch.zeros((8, 4), dtype=torch.float64).pin_memory()
-        self._result_next = 0
 
     # ------------------------------------------------------------------ initial condition
     def initialize(self, field: Optional[np.ndarray] = None) -> None:
@@ -578,13 +596,16 @@ class Solver:
     def _enqueue_result(self, st: RunStats) -> PendingResult:
         """One asynchronous 32-byte copy of the plan's result block into a pinned slot + one event."""
         from .ops import _lib
-        slot = self._result_pool[self._result_next % self._result_pool.shape[0]]
-        self._result_next += 1
+        ring = self.__dict__.get("_result_ring")
+        if ring is None:
+            ring = self._result_ring = _ResultRing(self._result_pool.shape[0])
+        idx = ring.claim()      # settles the handle that still owns the slot, if any
+        slot = self._result_pool[idx]
         _lib.check(self._lib.mcp_fused2d_result_async(self._plan, slot.data_ptr(), self._stream()),
                    "mcp_fused2d_result_async")
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.ctx.device))
-        return PendingResult(self, slot, ev, st)
+        return ring.bind(idx, PendingResult(self, slot, ev, st))
 
     def _decode_result(self, slot: torch.Tensor, st: RunStats) -> float:
         from .ops import _lib
@@ -607,7 +628,7 @@ class Solver:
     def run_async(self, generations: Optional[int] = None) -> PendingResult:
         """Enqueue a solve of ``generations`` generations (one launch, fused residual of the last generation) and
         return without waiting; ``.wait()`` on the returned handle yields the global residual and raises if the kernel
-        recorded an error.  Up to 8 solves may be pending.  Backends without an in-kernel residual run synchronously."""
+        recorded an error.  Eight result slots: enqueueing a ninth solve first waits for the oldest.  Backends without an in-kernel residual run synchronously."""
         g = self.cfg.generations if generations is None else int(generations)
         fused2d = self.backend == "fused" and self.ndim == 2
         if fused2d:

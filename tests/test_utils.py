@@ -55,3 +55,28 @@ def test_solver_dispatches_through_the_workload_registry():
     cfg = RunConfig(workload="mdf", height=9, width=7, backend="cpu")
     with Solver(cfg) as s:
         assert s._fix_bounds == (1, 7, 1, 5)
+
+
+def test_result_ring_settles_the_handle_that_still_owns_a_slot():
+    """Solver.run_async hands out 8 pinned result slots in a ring; a ninth enqueue must read the oldest handle's value
+    out before the slot is overwritten (solver._ResultRing; no counterpart in the reference, which has no results)."""
+    from mpi_cuda_process_b200.solver import _ResultRing
+
+    class Handle:
+        def __init__(self, log, name):
+            self.log, self.name, self.waited = log, name, False
+
+        def wait(self):
+            if not self.waited:
+                self.waited = True
+                self.log.append(self.name)
+
+    log, ring, handles = [], _ResultRing(4), []
+    for i in range(10):
+        idx = ring.claim()
+        assert idx == i % 4
+        handles.append(ring.bind(idx, Handle(log, i)))
+        if i == 1:
+            handles[1].wait()                       # a handle the caller has already waited for is not touched again
+    assert log == [1, 0, 2, 3, 4, 5]                # 0 settled when slot 0 came round (i=4), 2 at i=6, ...
+    assert [h.waited for h in handles] == [True] * 6 + [False] * 4
