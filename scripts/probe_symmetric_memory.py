@@ -1,3 +1,6 @@
+"""Does torch's symmetric memory rendezvous work on this box, and does it expose a multicast (NVLS) mapping?  Run under
+torchrun, one rank per GPU; the answer decides whether extra={"residual_allreduce": "nvls"} is available
+(solver.py::_ensure_plan).  Diagnostic only -- nothing imports this."""
 import os, torch, torch.distributed as dist
 import torch.distributed._symmetric_memory as sm
 rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"])
