@@ -67,6 +67,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--interior", type=float, default=0.0)
     p.add_argument("--halo-message", choices=["row", "element"], default="row")
     p.add_argument("--strict-fp64-accum", action="store_true")
+    p.add_argument("--input", default=None,
+                   help="initial field from a file (any --output-format; every rank reads it and keeps its block); the "
+                        "reference can only start from its built-in field (MDF_kernel.cu:146)")
+    p.add_argument("--input-format", choices=["ascii", "npy", "raw", "text"], default=None)
     p.add_argument("--output", default=None, help="write the final field here (rank 0)")
     p.add_argument("--output-format", choices=["ascii", "npy", "raw", "text"], default=None)
     p.add_argument("--print", dest="print_field", action="store_true",
@@ -112,9 +116,16 @@ def main(argv: Optional[List[str]] = None) -> int:
         checkpoint_dir=args.checkpoint_dir)
 
     rc = 0
+    start = None
     with Solver(cfg, ctx=ctx) as solver:
         if args.resume:
             ckpt.load(solver, args.resume)
+        elif args.input:
+            fmt = args.input_format or ("npy" if args.input.endswith(".npy") else cfg.output_format)
+            start = mio.load_field(args.input, fmt, shape=cfg.shape, dtype=solver.npdtype, w=cfg.width)
+            if tuple(start.shape) != tuple(cfg.shape):
+                raise SystemExit(f"--input holds a field of shape {tuple(start.shape)}, the run is {tuple(cfg.shape)}")
+            solver.initialize(start.astype(solver.npdtype, copy=False))
         else:
             solver.initialize()
         if cfg.tol is not None:
@@ -148,7 +159,7 @@ def main(argv: Optional[List[str]] = None) -> int:
             if args.output and field is not None:
                 mio.dump_field(field, args.output, cfg.output_format)
             if args.check and field is not None:
-                ref = oracle.run_field(cfg, oracle.init_field(cfg), solver.generation)
+                ref = oracle.run_field(cfg, start if start is not None else oracle.init_field(cfg), solver.generation)
                 same = bool((ref == field).all())
                 print(f"oracle check: {'bitwise equal' if same else 'MISMATCH'} after {solver.generation} generations")
                 rc = 0 if same else 1

@@ -87,3 +87,28 @@ def test_cli_logs_jsonl(tmp_path):
     assert r.returncode == 0, r.stderr
     rec = json.loads(log.read_text().splitlines()[-1])
     assert rec["workload"] == "mdf" and rec["generations"] == 3 and "ts" in rec
+
+
+def test_cli_continues_from_an_input_file(tmp_path):
+    """--input: start from a field written by --output (the reference can only start from create_universe,
+    MDF_kernel.cu:146); 3 + 4 generations through a print_array file equal 7 generations of the oracle."""
+    first, second = tmp_path / "g3.txt", tmp_path / "g7.txt"
+    base = [sys.executable, "-m", "mpi_cuda_process_b200", "--workload", "life", "--backend", "cpu", "--no-prompt",
+            "--height", "12", "--width", "10"]
+    r = subprocess.run(base + ["-g", "3", "--output", str(first)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run(base + ["-g", "4", "--input", str(first), "--output", str(second), "--check"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "bitwise equal after 4 generations" in r.stdout
+    assert second.read_bytes() == mio.format_array(oracle.life_run(oracle.life_init_reference(12, 10), 7))
+    # float field through .npy; a file of the wrong shape is refused
+    npy = tmp_path / "u.npy"
+    np.save(npy, oracle.mdf_run(oracle.mdf_init(9, 11), 2))
+    mdf = [sys.executable, "-m", "mpi_cuda_process_b200", "--workload", "mdf", "--backend", "cpu", "--no-prompt",
+           "-g", "5", "--input", str(npy), "--output", str(tmp_path / "u7.npy")]
+    r = subprocess.run(mdf + ["--height", "9", "--width", "11"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert np.load(tmp_path / "u7.npy").tobytes() == oracle.mdf_run(oracle.mdf_init(9, 11), 7).tobytes()
+    r = subprocess.run(mdf + ["--height", "10", "--width", "11"], capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0 and "shape" in (r.stderr + r.stdout)
