@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import os
 import sys
 from typing import List, Optional
 
@@ -75,6 +76,11 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--output-format", choices=["ascii", "npy", "raw", "text"], default=None)
     p.add_argument("--print", dest="print_field", action="store_true",
                    help="print the final life grid in the reference's print_array format")
+    p.add_argument("--print-every", type=int, default=0, metavar="N",
+                   help="print the grid every N generations -- the per-generation print_array calls the reference "
+                        "carries commented out inside its loop (kernel.cu:232,265)")
+    p.add_argument("--output-every", type=int, default=0, metavar="N",
+                   help="also write a frame every N generations: <output stem>.gNNNNNN<ext>")
     p.add_argument("--check", action="store_true", help="compare with the CPU oracle (small grids)")
     p.add_argument("--json", action="store_true", help="print run statistics as one JSON line")
     p.add_argument("--log-jsonl", default=None, help="append run statistics as JSON lines to this file (rank 0)")
@@ -128,36 +134,62 @@ def main(argv: Optional[List[str]] = None) -> int:
             solver.initialize(start.astype(solver.npdtype, copy=False))
         else:
             solver.initialize()
+
+        def emit(print_it: bool, path: Optional[str]) -> Optional["np.ndarray"]:
+            """Collective: gather on every rank, print / write on rank 0.  Returns the gathered field (rank 0)."""
+            life = cfg.workload == "life"
+            need_field = bool(path) or (print_it and not life)
+            fld = solver.gather() if need_field else None
+            text = solver.gather_ascii() if (print_it and life) else None
+            if ctx.rank == 0:
+                if text is not None:
+                    sys.stdout.flush()
+                    sys.stdout.buffer.write(text)
+                    sys.stdout.buffer.flush()
+                elif print_it and fld is not None:
+                    mio.print_array(fld)
+                if path and fld is not None:
+                    mio.dump_field(fld, path, cfg.output_format)
+            return fld
+
+        def frame_path(generation: int) -> Optional[str]:
+            if not args.output:
+                return None
+            stem, ext = os.path.splitext(args.output)
+            return f"{stem}.g{generation:06d}{ext}"
+
+        ckpt_every = cfg.checkpoint_every if cfg.checkpoint_dir else 0
+        periods = [n for n in (ckpt_every, args.print_every, args.output_every if args.output else 0) if n > 0]
         if cfg.tol is not None:
             stats = solver.run_to_tolerance()
-        elif cfg.checkpoint_every > 0 and cfg.checkpoint_dir:
+        elif periods:
+            # segments end at every multiple of a period (generations counted from this run's start)
             from .solver import RunStats
             stats = RunStats(cells=cfg.cells)
-            left = g
-            while left > 0:
-                n = min(cfg.checkpoint_every, left)
+            done = 0
+            while done < g:
+                n = min(min((done // q + 1) * q for q in periods), g) - done
                 s = solver.run(n, residual=cfg.residual != "none")
                 stats.generations += n
                 stats.device_ms += s.device_ms
                 stats.launches += s.launches
                 stats.residual_history += s.residual_history
-                left -= n
-                ckpt.save(solver, cfg.checkpoint_dir)
+                done += n
+                if ckpt_every and (done % ckpt_every == 0 or done == g):
+                    ckpt.save(solver, cfg.checkpoint_dir)
+                want_print = args.print_every > 0 and done % args.print_every == 0 and done < g
+                want_frame = args.output_every > 0 and done % args.output_every == 0
+                if want_print or (want_frame and args.output):
+                    emit(want_print, frame_path(done) if want_frame else None)
         else:
             stats = solver.run(g, residual=cfg.residual != "none")
         solver.check_status()
-        need_field = bool(args.output or args.check or (args.print_field and cfg.workload != "life"))
-        field = solver.gather() if need_field else None
-        ascii_bytes = solver.gather_ascii() if (args.print_field and cfg.workload == "life") else None
+        final_print = args.print_field or args.print_every > 0
+        field = emit(final_print, args.output)
+        gathered = bool(args.output) or (final_print and cfg.workload != "life")
+        if args.check and not gathered:        # decided from the flags: the gather is collective, `field` is rank 0's
+            field = solver.gather()
         if ctx.rank == 0:
-            if ascii_bytes is not None:
-                sys.stdout.flush()
-                sys.stdout.buffer.write(ascii_bytes)
-                sys.stdout.buffer.flush()
-            elif args.print_field and field is not None:
-                mio.print_array(field)
-            if args.output and field is not None:
-                mio.dump_field(field, args.output, cfg.output_format)
             if args.check and field is not None:
                 ref = oracle.run_field(cfg, start if start is not None else oracle.init_field(cfg), solver.generation)
                 same = bool((ref == field).all())

@@ -112,3 +112,22 @@ def test_cli_continues_from_an_input_file(tmp_path):
     assert np.load(tmp_path / "u7.npy").tobytes() == oracle.mdf_run(oracle.mdf_init(9, 11), 7).tobytes()
     r = subprocess.run(mdf + ["--height", "10", "--width", "11"], capture_output=True, text=True, timeout=300)
     assert r.returncode != 0 and "shape" in (r.stderr + r.stdout)
+
+
+def test_cli_prints_and_writes_frames_every_n_generations(tmp_path):
+    """--print-every: the reference's per-generation print_array calls (commented out in its loop, kernel.cu:232,265);
+    --output-every: the same as files."""
+    out = tmp_path / "life.txt"
+    r = subprocess.run([sys.executable, "-m", "mpi_cuda_process_b200", "--workload", "life", "--backend", "cpu",
+                        "--no-prompt", "-g", "5", "--height", "9", "--width", "8", "--print-every", "2",
+                        "--output-every", "2", "--output", str(out), "--check"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    u0 = oracle.life_init_reference(9, 8)
+    frames = [mio.format_array(oracle.life_run(u0, g)).decode() for g in (2, 4, 5)]
+    pos = [r.stdout.index(f) for f in frames]            # generations 2 and 4 in the loop, 5 at the end, in order
+    assert pos == sorted(pos)
+    assert (tmp_path / "life.g000002.txt").read_bytes() == frames[0].encode()
+    assert (tmp_path / "life.g000004.txt").read_bytes() == frames[1].encode()
+    assert out.read_bytes() == frames[2].encode()
+    assert "bitwise equal after 5 generations" in r.stdout
