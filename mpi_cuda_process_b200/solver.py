@@ -537,6 +537,12 @@ class Solver:
         self.total_stats.halo_messages += st.halo_messages
         return st
 
+    def step(self, residual=False) -> RunStats:
+        """One generation -- one trip through the reference's loop body (MDF_kernel.cu:157-187).  On the fused 2-D
+        backend a launch advances whole time blocks, so single steps run the TB = 1 instantiation; prefer
+        :meth:`run` with the full count."""
+        return self.run(1, residual=residual)
+
     # -- fused ---------------------------------------------------------------------------------
     def _run_fused3d(self, g: int, residual: bool, st: RunStats) -> None:
         """One launch; the residual (every generation, or the last one for residual="final") is accumulated by the

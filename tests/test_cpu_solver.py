@@ -138,3 +138,16 @@ def test_checksum_is_decomposition_independent():
         s.initialize()
         s.run(6)
         assert s.checksum() == whole
+
+
+def test_step_is_one_trip_through_the_reference_loop():
+    """Solver.step(): one generation (MDF_kernel.cu:157-187); n steps equal run(n) and count generations."""
+    cfg = RunConfig(workload="mdf", height=11, width=13, backend="cpu", residual="linf")
+    with Solver(cfg) as a, Solver(cfg) as b:
+        a.initialize()
+        b.initialize()
+        for _ in range(5):
+            st = a.step(residual=True)
+        b.run(5)
+        assert a.generation == b.generation == 5 and st.generations == 1 and len(st.residual_history) == 1
+        assert a.gather().tobytes() == b.gather().tobytes() == oracle.mdf_run(oracle.mdf_init(11, 13), 5).tobytes()
