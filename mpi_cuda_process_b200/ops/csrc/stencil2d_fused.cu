@@ -1195,7 +1195,9 @@ int mcp_fused2d_create(const mcp_fused2d_desc* desc, mcp_fused2d_plan** plan_out
     if (d.strip_flags != nullptr) {
         MCP_REQUIRE(!d.up_buf[0] || d.up_strip_flag, "up_strip_flag required with strip_flags and up_buf");
         MCP_REQUIRE(!d.dn_buf[0] || d.dn_strip_flag, "dn_strip_flag required with strip_flags and dn_buf");
-        MCP_REQUIRE(ceil_div(d.w, outw_rt(d.dtype, 1)) <= kMaxStripFlags, "grid too wide for per-strip halo flags");
+        // strips are narrowest (most numerous) at the largest time block this plan can run
+        MCP_REQUIRE(ceil_div(d.w, outw_rt(d.dtype, std::min(max_tb(d.op, d.dtype), d.ghost))) <= kMaxStripFlags,
+                    "grid too wide for per-strip halo flags");
     }
     MCP_REQUIRE(d.chunk_rows >= 0, "negative chunk_rows");
 
