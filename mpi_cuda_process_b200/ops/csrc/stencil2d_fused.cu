@@ -1166,6 +1166,15 @@ int choose_mode(const mcp_fused2d_plan* pl, int tb, bool every_sweep_residual) {
     return 1;
 }
 
+// The time block a run with the requested value executes first: the largest power of two within the request, the
+// operator's limit and the ghost depth (the rule of run_impl), so that the introspection calls describe that schedule.
+int effective_tb(const mcp_fused2d_plan* pl, int time_block) {
+    const int tbmax = std::min(max_tb(pl->d.op, pl->d.dtype), pl->d.ghost);
+    int tb = 1;
+    while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
+    return tb;
+}
+
 }  // namespace
 
 extern "C" {
@@ -1291,6 +1300,7 @@ int mcp_fused2d_set_option(mcp_fused2d_plan* pl, int option, long long value) {
 int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_strips, int* n_chunks, int* grid,
                          int* smem_bytes) {
     MCP_REQUIRE(pl, "null plan");
+    time_block = effective_tb(pl, time_block);
     const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     if (n_strips) *n_strips = g.n_strips;
     if (n_chunks) *n_chunks = g.n_chunks();
@@ -1302,6 +1312,7 @@ int mcp_fused2d_geometry(const mcp_fused2d_plan* pl, int time_block, int* n_stri
 // Heights of the row chunks (= tiles) of the default schedule, in slab order.
 int mcp_fused2d_chunks(const mcp_fused2d_plan* pl, int time_block, int* rows_out, int max_entries) {
     MCP_REQUIRE(pl && rows_out, "null argument");
+    time_block = effective_tb(pl, time_block);
     const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     const int n = std::min(g.n_chunks(), max_entries);
     for (int i = 0; i < n; ++i) rows_out[i] = g.chunk_y[i + 1] - g.chunk_y[i];
@@ -1332,10 +1343,7 @@ static int launch(mcp_fused2d_plan* pl, const LaunchSpec& ls, cudaStream_t strea
 
 static int run_impl(mcp_fused2d_plan* pl, int generations, int time_block, int residual_mode, int stop_mode,
                     double stop_thresh, cudaStream_t stream) {
-    const mcp_fused2d_desc& d = pl->d;
-    const int tbmax = std::min(max_tb(d.op, d.dtype), d.ghost);
-    int tb = 1;
-    while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
+    int tb = effective_tb(pl, time_block);
     if (residual_mode != MCP_RES_NONE) pl->res_slots_used = 0;
     pl->last_generations = 0;
     pl->last_stop_reason = MCP_STOP_NONE;
@@ -1424,9 +1432,7 @@ int mcp_fused2d_run_group(mcp_fused2d_plan** plans, int n, int generations, int 
     cudaStream_t stream = (cudaStream_t)stream_;
     mcp_fused2d_plan* p0 = plans[0];
     MCP_REQUIRE(p0, "null plan");
-    const int tbmax = std::min(max_tb(p0->d.op, p0->d.dtype), p0->d.ghost);
-    int tb = 1;
-    while (tb * 2 <= time_block && tb * 2 <= tbmax) tb *= 2;
+    const int tb = effective_tb(p0, time_block);
     MCP_REQUIRE(generations >= tb && generations % tb == 0, "generations must be a positive multiple of the time block");
     MCP_REQUIRE(residual_mode == MCP_RES_NONE || residual_mode == MCP_RES_LAST || residual_mode == MCP_RES_FINAL,
                 "bad residual mode");
@@ -1524,6 +1530,7 @@ int mcp_fused2d_plan_schedule(int op, int dtype, int w, int rows_own, int ghost,
 // that a host tool can see which tiles are the critical path and where ranks wait for each other.
 int mcp_fused2d_tile_trace2(mcp_fused2d_plan* pl, int time_block, int which, uint32_t* ns_out, int max_entries) {
     MCP_REQUIRE(pl && ns_out && which >= 0 && which <= 2, "bad argument");
+    time_block = effective_tb(pl, time_block);
     const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     const int n = std::min(std::min(g.n_strips * g.n_chunks(), pl->last_tiles), max_entries);
     if (n > 0)
@@ -1535,6 +1542,7 @@ int mcp_fused2d_tile_trace2(mcp_fused2d_plan* pl, int time_block, int which, uin
 int mcp_fused2d_tile_trace(mcp_fused2d_plan* pl, int time_block, uint32_t* ns_out, int* chunk_out, int* strip_out,
                            int max_entries) {
     MCP_REQUIRE(pl && ns_out, "null argument");
+    time_block = effective_tb(pl, time_block);
     const Geometry& g = pl->geo[tb_index(time_block)][choose_mode(pl, time_block, false)];
     const int nstr = g.n_strips, ng = g.n_chunks();
     const int n = std::min(std::min(nstr * ng, pl->last_tiles), max_entries);
