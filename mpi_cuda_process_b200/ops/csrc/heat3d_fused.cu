@@ -526,6 +526,18 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
     MCP_REQUIRE(d.pitch >= d.w && d.pitch % 32 == 0, "pitch must be a multiple of 32 and >= w");
     MCP_REQUIRE(d.py_alloc >= d.ny + 2 && d.pz_alloc >= d.nz + 2, "allocation smaller than block + ghost layers");
     MCP_REQUIRE(d.buf[0] && d.buf[1], "null buffer");
+    for (int f = 0; f < 4; ++f) {
+        MCP_REQUIRE((d.nbr_buf[f][0] == nullptr) == (d.nbr_buf[f][1] == nullptr), "nbr_buf[%d] must be both set or both null", f);
+        if (d.nbr_buf[f][0] != nullptr)
+            MCP_REQUIRE(d.flags != nullptr && d.nbr_flag[f] != nullptr && d.expect[f] >= 1 && d.nbr_n[f] >= 1,
+                        "neighbour %d needs flags, nbr_flag, expect >= 1 and nbr_n >= 1", f);
+    }
+    // tile counts first: nothing is allocated yet if the block does not fit the tile encoding
+    const int zchunk = d.zchunk > 0 ? d.zchunk : 64;
+    const int nsx = (int)ceil_div(d.w, 32 * vec3(d.dtype));
+    const int nby = (int)ceil_div(d.ny, k3TileRows);
+    const int nzc = (int)ceil_div(d.nz, zchunk);
+    MCP_REQUIRE(nsx < 1024 && nby < 1024 && nzc < 2048, "block too large for the tile encoding");
     mcp_fused3d_plan* pl = new (std::nothrow) mcp_fused3d_plan();
     MCP_REQUIRE(pl, "out of host memory");
     pl->d = d;
@@ -546,7 +558,7 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
     int rc = device_sm_count(&sm);
     if (rc) { delete pl; return rc; }
     pl->grid = 2 * sm;
-    pl->zchunk = d.zchunk > 0 ? d.zchunk : 64;
+    pl->zchunk = zchunk;
 
     const int esz = d.dtype == MCP_DTYPE_F64 ? 8 : 4;
     for (int b = 0; b < 2; ++b) {
@@ -557,10 +569,6 @@ int mcp_fused3d_create(const mcp_fused3d_desc* desc, mcp_fused3d_plan** plan_out
         if (rc) { delete pl; return rc; }
     }
     // tile list, pencil-face tiles first so their pushes overlap the interior
-    const int nsx = (int)ceil_div(d.w, 32 * vec3(d.dtype));
-    const int nby = (int)ceil_div(d.ny, k3TileRows);
-    const int nzc = (int)ceil_div(d.nz, pl->zchunk);
-    MCP_REQUIRE(nsx < 1024 && nby < 1024 && nzc < 2048, "block too large for the tile encoding");
     std::vector<int> face, inner;
     for (int zc = 0; zc < nzc; ++zc)
         for (int by = 0; by < nby; ++by)
