@@ -97,7 +97,12 @@ int mcp_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* total_m
 int mcp_arena_alloc(size_t bytes, void** ptr) {
     MCP_REQUIRE(ptr && bytes > 0, "mcp_arena_alloc: bad arguments");
     MCP_CUDA_TRY(cudaMalloc(ptr, bytes));
-    MCP_CUDA_TRY(cudaMemset(*ptr, 0, bytes));
+    cudaError_t e = cudaMemset(*ptr, 0, bytes);
+    if (e != cudaSuccess) {
+        cudaFree(*ptr);
+        *ptr = nullptr;
+        MCP_CUDA_TRY(e);
+    }
     return MCP_OK;
 }
 
@@ -109,6 +114,7 @@ int mcp_arena_free(void* ptr) {
 int mcp_ipc_handle_size(void) { return (int)sizeof(cudaIpcMemHandle_t); }
 
 int mcp_ipc_get_handle(void* ptr, void* handle_out) {
+    MCP_REQUIRE(ptr && handle_out, "mcp_ipc_get_handle: null argument");
     cudaIpcMemHandle_t h;
     MCP_CUDA_TRY(cudaIpcGetMemHandle(&h, ptr));
     memcpy(handle_out, &h, sizeof(h));
@@ -116,6 +122,7 @@ int mcp_ipc_get_handle(void* ptr, void* handle_out) {
 }
 
 int mcp_ipc_open_handle(const void* handle, void** ptr_out) {
+    MCP_REQUIRE(handle && ptr_out, "mcp_ipc_open_handle: null argument");
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, sizeof(h));
     MCP_CUDA_TRY(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
