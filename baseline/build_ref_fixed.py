@@ -4,7 +4,8 @@ against the MPI stand-in of ``mpi_shim/``.
 
     python baseline/build_ref_fixed.py            ->  baseline/_ref/ref_fixed  (git-ignored; travels with gpurun)
 
-The patch is kept as a diff against /root/reference/MDF_kernel.cu (CRLF preserved).  What it changes, and nothing
+The patch is kept as a zero-context unified diff against /root/reference/MDF_kernel.cu (CRLF preserved; the
+unmodified file is the only thing it can apply to, so no context lines are carried).  What it changes, and nothing
 else: the ``create_universe`` call (MDF_kernel.cu:146 vs :88), one loop for every rank with mirrored peers and offsets
 (:155-222; N row slabs instead of the hard-wired two), the new field is what comes back from the GPU (:164,177), the
 Dirichlet ring is held and the out-of-bounds neighbour reads are gone (:13-20,30-31), cells that are not a rank's own
