@@ -14,7 +14,8 @@ Rank 0 prints ONE JSON line.  ``value`` is device-timed (CUDA events around the 
 ``e2e`` repeats the measurement through the public API with a pinned-host -> device upload of the rank's slab
 and a device -> host read of the step's result (kernel status + global residual of the last iteration) inside every
 step; ``e2e_with_gather`` additionally assembles the solution field on rank 0 (fused gather + pack over NVLink) and
-copies it to pinned host memory every step.
+copies it to pinned host memory every step.  Each rank binds itself to the CPUs next to its GPU first (so that pinned
+buffers come from the GPU's memory node; ``--no-numa-bind`` switches that off; recorded under ``config``).
 ``--impl reference`` is the reference arm (the reference cannot be built or run here).
 """
 from __future__ import annotations
@@ -56,6 +57,8 @@ def parse_args(argv=None):
     p.add_argument("--cluster3d", action="store_true", help="--impl nccl --workload heat3d: the cluster/DSMEM kernel")
     p.add_argument("--e2e-depth", type=int, default=1, help="steps enqueued ahead of the result being read (e2e)")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-numa-bind", action="store_true",
+                   help="do not bind each rank to the CPUs (and memory node) next to its GPU")
     p.add_argument("--halo-message", default="row", choices=["row", "element"])
     p.add_argument("--coarse-halo-flags", action="store_true", help="one arrival counter per neighbour instead of per-strip flags")
     return p.parse_args(argv)
@@ -95,6 +98,9 @@ def main(argv=None) -> int:
     from mpi_cuda_process_b200.utils import metrics
 
     ctx = init_context(device="cuda")
+    # host side next to the GPU before the first pinned allocation (torchrun does not bind its children)
+    from mpi_cuda_process_b200.utils import numa
+    numa_rec = {"bound": False, "why": "disabled"} if args.no_numa_bind else numa.bind_to_gpu(ctx.device.index or 0)
     if ctx.world != args.gpus and ctx.rank == 0:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE={ctx.world}", file=sys.stderr)
     backend = {"ours": "fused"}.get(args.impl, args.impl)
@@ -261,7 +267,8 @@ def main(argv=None) -> int:
                            "iterations": gps * K, "parallelism": f"{args.decomposition}{ctx.world}",
                            "time_block": s.time_block, "backend": s.backend,
                            "l2": "inputs larger than L2 (two %d MiB buffers per GPU stream through HBM every pass)"
-                                 % (int(cells_gpu * esize) >> 20), "geometry": geom},
+                                 % (int(cells_gpu * esize) >> 20), "geometry": geom,
+                           "host_affinity_rank0": numa_rec},
                 "gpu_launches": int(launches),
                 "clocks": clocks,
                 "roofline": {k: (round(v, 4) if isinstance(v, float) else v) for k, v in roof.items()},

@@ -80,3 +80,33 @@ def test_result_ring_settles_the_handle_that_still_owns_a_slot():
             handles[1].wait()                       # a handle the caller has already waited for is not touched again
     assert log == [1, 0, 2, 3, 4, 5]                # 0 settled when slot 0 came round (i=4), 2 at i=6, ...
     assert [h.waited for h in handles] == [True] * 6 + [False] * 4
+
+
+def test_numa_binding_from_fake_sysfs(tmp_path):
+    """utils/numa.py: CPU affinity from the GPU's PCI locality (best effort, never raises).  No counterpart in the
+    reference, where every rank shares GPU 0 (MDF_kernel.cu:114-121)."""
+    import os
+    from mpi_cuda_process_b200.utils import numa
+    assert numa.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert numa.parse_cpulist("") == set()
+    allowed = sorted(os.sched_getaffinity(0))
+    dev = tmp_path / "0000:1b:00.0"
+    dev.mkdir()
+    (dev / "numa_node").write_text("1\n")
+    try:
+        # a cpulist that holds exactly one allowed CPU: the process ends up bound to it
+        (dev / "local_cpulist").write_text(f"{allowed[0]}\n")
+        rec = numa.bind_to_gpu(0, sysfs=str(tmp_path), pci="0000:1b:00.0")
+        assert rec["bound"] and rec["numa_node"] == 1 and rec["cpus"] == 1
+        assert os.sched_getaffinity(0) == {allowed[0]}
+    finally:
+        os.sched_setaffinity(0, allowed)
+    # CPUs outside the cpuset, a missing device and a missing file are reported, not raised
+    (dev / "local_cpulist").write_text("100000-100003\n")
+    assert numa.bind_to_gpu(0, sysfs=str(tmp_path), pci="0000:1b:00.0")["bound"] is False
+    assert numa.bind_to_gpu(0, sysfs=str(tmp_path), pci="0000:ff:00.0")["bound"] is False
+    assert os.sched_getaffinity(0) == set(allowed)
+    # every CPU local (single node): nothing to change
+    (dev / "local_cpulist").write_text(",".join(str(c) for c in allowed) + "\n")
+    rec = numa.bind_to_gpu(0, sysfs=str(tmp_path), pci="0000:1b:00.0")
+    assert rec["bound"] and "already local" in rec["why"]
