@@ -47,27 +47,40 @@ def build_parser() -> argparse.ArgumentParser:
     from . import models
     p.add_argument("--workload", choices=sorted(models.REGISTRY), default="mdf",
                    help="; ".join(f"{w.name}: {w.description}" for w in models.REGISTRY.values()))
-    p.add_argument("-g", "--generations", type=int, default=None)
-    p.add_argument("--height", type=int, default=None)
-    p.add_argument("--width", type=int, default=None)
-    p.add_argument("--depth", type=int, default=0)
+    p.add_argument("-g", "--generations", type=int, default=None, help="generations to run (else read from stdin)")
+    p.add_argument("--height", type=int, default=None, help="rows of the grid (else read from stdin)")
+    p.add_argument("--width", type=int, default=None, help="columns of the grid (else read from stdin)")
+    p.add_argument("--depth", type=int, default=0, help="planes of the grid (heat3d)")
     p.add_argument("--dtype", choices=["fp32", "fp64", "bits"], default="fp32",
                    help="bits = bit-packed life cells (fused GPU backend)")
-    p.add_argument("--bc", choices=["fixed-ring", "dead-outside"], default=None)
-    p.add_argument("--backend", choices=["auto", "fused", "nccl", "staged", "cpu"], default="auto")
-    p.add_argument("--decomposition", choices=["slab", "pencil"], default="slab")
-    p.add_argument("--pencil", type=int, nargs=2, default=(0, 0), metavar=("PZ", "PY"))
-    p.add_argument("--time-block", type=int, default=8)
+    p.add_argument("--bc", choices=["fixed-ring", "dead-outside"], default=None,
+                   help="life: hold the outer ring, or treat cells outside the grid as dead (default); mdf and heat3d "
+                        "always hold their boundary")
+    p.add_argument("--backend", choices=["auto", "fused", "nccl", "staged", "cpu"], default="auto",
+                   help="fused = the persistent sm_100a kernel (default on GPUs); nccl / staged = baselines; cpu = "
+                        "torch CPU + gloo")
+    p.add_argument("--decomposition", choices=["slab", "pencil"], default="slab",
+                   help="slab = cut the first axis; pencil = cut z and y of a 3-D grid")
+    p.add_argument("--pencil", type=int, nargs=2, default=(0, 0), metavar=("PZ", "PY"),
+                   help="ranks along z and y for --decomposition pencil (0 0 = choose)")
+    p.add_argument("--time-block", type=int, default=8,
+                   help="generations per pass over the field in the fused 2-D kernel (1, 2, 4, 8)")
     p.add_argument("--tol", type=float, default=None, help="run to tolerance on the global residual")
-    p.add_argument("--max-generations", type=int, default=0)
-    p.add_argument("--residual", choices=["none", "l2", "linf"], default="none")
-    p.add_argument("--seed", type=int, default=None)
-    p.add_argument("--prob", type=float, default=0.15)
+    p.add_argument("--max-generations", type=int, default=0, help="upper bound for --tol runs")
+    p.add_argument("--residual", choices=["none", "l2", "linf"], default="none",
+                   help="norm of u' - u to report (and to compare with --tol)")
+    p.add_argument("--seed", type=int, default=None,
+                   help="life: counter-based random universe (default: the reference's unseeded glibc rand() stream); "
+                        "mdf --init hash: seed of the random interior")
+    p.add_argument("--prob", type=float, default=0.15, help="life: probability that a cell starts alive (kernel.cu:193)")
     p.add_argument("--init", choices=["ring", "hash", "box"], default="ring", help="mdf initial field")
-    p.add_argument("--ring", type=float, default=100.0)
-    p.add_argument("--interior", type=float, default=0.0)
-    p.add_argument("--halo-message", choices=["row", "element"], default="row")
-    p.add_argument("--strict-fp64-accum", action="store_true")
+    p.add_argument("--ring", type=float, default=100.0, help="boundary value (MDF_kernel.cu:93)")
+    p.add_argument("--interior", type=float, default=0.0, help="initial interior value")
+    p.add_argument("--halo-message", choices=["row", "element"], default="row",
+                   help="staged baseline: one message per border row, or the reference's one per element")
+    p.add_argument("--strict-fp64-accum", action="store_true",
+                   help="unfused backends: evaluate the last step of the update in fp64 like the reference's SASS "
+                        "(bit-identical to the default)")
     p.add_argument("--input", default=None,
                    help="initial field from a file (any --output-format; every rank reads it and keeps its block); the "
                         "reference can only start from its built-in field (MDF_kernel.cu:146)")
@@ -85,8 +98,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--json", action="store_true", help="print run statistics as one JSON line")
     p.add_argument("--log-jsonl", default=None, help="append run statistics as JSON lines to this file (rank 0)")
     p.add_argument("--no-prompt", action="store_true", help="do not read g/h/w from stdin (flags only)")
-    p.add_argument("--checkpoint-dir", default=None)
-    p.add_argument("--checkpoint-every", type=int, default=0)
+    p.add_argument("--checkpoint-dir", default=None, help="write checkpoints (one file per rank + manifest) here")
+    p.add_argument("--checkpoint-every", type=int, default=0, help="generations between checkpoints")
     p.add_argument("--resume", default=None, help="checkpoint directory to resume from")
     return p
 
