@@ -82,3 +82,19 @@ def test_the_drain_is_only_needed_for_uploads(flags, sync):
     # launches that continue from the previous state are ordered by the sequence flags alone
     r = explore(seeds=100, flags=flags, sync=sync, drain=False, upload=False, **MULTI)
     assert r["violations"] == 0, r.get("first")
+
+
+def test_random_geometries_property():
+    """Hypothesis over ranks x chunks x strips x warps x sweeps x launches: the two combinations the kernel runs stay
+    sound; shrinks to a minimal geometry + seed if they ever do not."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(ranks=st.integers(1, 4), chunks=st.integers(1, 5), strips=st.integers(1, 5), warps=st.integers(1, 5),
+           sweeps=st.integers(1, 4), launches=st.integers(1, 3), seed=st.integers(0, 10**6),
+           combo=st.sampled_from([("strip", "dataflow"), ("coarse", "barrier"), ("strip", "barrier")]))
+    def run(ranks, chunks, strips, warps, sweeps, launches, seed, combo):
+        Model(ranks=ranks, chunks=chunks, strips=strips, warps=warps, sweeps=sweeps, launches=launches,
+              flags=combo[0], sync=combo[1], seed=seed, stall_rate=0.05, max_stall=200).run()
+
+    run()
