@@ -14,7 +14,9 @@ arrival counter cannot tell a barrier-free neighbour's sweeps apart); the model 
 milliseconds.  ``launches`` > 1 models back-to-back kernels with no host barrier between the ranks; with ``upload``
 the host overwrites the whole slab between launches (Solver.load_local / commit_input), which is only safe because a
 launch drains its incoming halo pushes before it ends (``drain=False`` shows the race; without uploads the sequence flags
-alone are enough).  The reference has no protocol to check: its only synchronisation is cudaDeviceSynchronize and blocking
+alone are enough).  Warps draw their next ticket when they start a tile (``lookahead``) and read that tile's input early
+when a non-blocking probe of its nine completion words succeeds (``prefetch``), as the kernel does; ``prefetch_ghost``
+is the variant the kernel avoids (prefetching a tile whose condition includes the neighbour GPU's flags).  The reference has no protocol to check: its only synchronisation is cudaDeviceSynchronize and blocking
 one-element MPI calls (MDF_kernel.cu:166-183), and its D2H -> send ordering holds by accident.
 """
 from __future__ import annotations
@@ -33,6 +35,9 @@ class _Warp:
     rank: int
     ticket: Optional[Tuple[int, int, int]] = None   # (sweep, chunk, strip)
     phase: int = 0                                   # 0 wait, 1 read, 2 write, 3 push, 4 signal, 5 publish
+    nxt: Optional[Tuple[int, int, int]] = None       # look-ahead ticket, drawn when the current tile starts
+    looked: bool = False                             # the look-ahead draw of the current tile has been attempted
+    pre: bool = False                                # the look-ahead tile's input has been read already (prefetch)
 
 
 @dataclass
@@ -47,6 +52,9 @@ class Model:
     launches: int = 1             # kernel launches per rank, `sweeps` sweeps each, NO host barrier between the ranks
     upload: bool = True           # between launches the host overwrites the whole slab (ghost rows included)
     drain: bool = True            # a launch ends only when every halo push addressed to this rank has landed
+    lookahead: bool = True        # a warp draws its next ticket when it starts a tile (grab() behind the current tile)
+    prefetch: bool = True         # ... and reads that tile's input early if a non-blocking probe finds it settled
+    prefetch_ghost: bool = False  # UNSOUND variant: prefetch also tiles that read ghost rows, probing tile_done only
     seed: int = 0
     stall_rate: float = 0.02      # probability per scheduler round that the adversary freezes a warp or a rank
     max_stall: int = 400          # longest freeze, in scheduler rounds
@@ -98,20 +106,23 @@ class Model:
                 return False
         return True
 
-    def _draw(self, w: _Warp) -> bool:
+    def _draw_ticket(self, r: int, transition: bool = True) -> Optional[Tuple[int, int, int]]:
+        """Next ticket of rank r, or None if none can be handed out now.  A launch boundary is crossed only with
+        ``transition`` (the look-ahead draw never crosses one: the kernel's ticket range ends with the launch)."""
         n_tiles = self.chunks * self.strips
-        r = w.rank
         t = self.next_ticket[r]
         if t >= self.launches * self.sweeps * n_tiles:
-            return False
+            return None
         g = t // n_tiles                                  # global sweep: seq_base + sw in the kernel
         launch = g // self.sweeps
         if launch > self.launched[r]:
+            if not transition:
+                return None
             # the previous kernel of this rank has to end first: all its tiles, then the drain; then the host's copy
             if any(self.finished[r][g2] < n_tiles for g2 in range(g)):
-                return False
+                return None
             if self.drain and not self._drained(r, g):
-                return False
+                return None
             if self.upload:
                 b, v = g & 1, self._tag(launch) + g
                 for c in range(self.chunks):
@@ -121,23 +132,26 @@ class Model:
                     for s in range(self.strips):
                         self.ghost[r][b][d][s] = v
             self.launched[r] = launch
-            return True
         if self.sync == "barrier" and g % self.sweeps > 0 and self.finished[r][g - 1] < n_tiles:
-            return False                                  # grid barrier: a sweep starts when the previous one is complete
+            return None                                   # grid barrier: a sweep starts when the previous one is complete
         self.next_ticket[r] = t + 1
         c, s = self.order[t % n_tiles]
-        w.ticket, w.phase = (g, c, s), 0
-        return True
+        return (g, c, s)
 
-    def _deps_ready(self, w: _Warp) -> bool:
-        r = w.rank
-        k, c, s = w.ticket
+    def _reads_ghost(self, r: int, ticket) -> bool:
+        _, c, _ = ticket
+        return (c == 0 and self._has(r, 0)) or (c == self.chunks - 1 and self._has(r, 1))
+
+    def _deps_ready(self, r: int, ticket, local_only: bool = False) -> bool:
+        k, c, s = ticket
         C, S = self.chunks, self.strips
         if self.sync == "dataflow" and k % self.sweeps > 0:
             for c2 in (c - 1, c, c + 1):
                 for s2 in (s - 1, s, s + 1):
                     if 0 <= c2 < C and 0 <= s2 < S and self.tile_done[r][c2][s2] < k:
                         return False
+        if local_only:
+            return True
         for d, edge in ((0, c == 0), (1, c == C - 1)):
             if edge and self._has(r, d) and k > 0:
                 if self.flags == "strip":
@@ -147,9 +161,8 @@ class Model:
                     return False
         return True
 
-    def _read(self, w: _Warp) -> None:
-        r = w.rank
-        k, c, s = w.ticket
+    def _read(self, r: int, ticket) -> None:
+        k, c, s = ticket
         C, S = self.chunks, self.strips
         b = k & 1
         for c2 in (c - 1, c, c + 1):
@@ -171,18 +184,37 @@ class Model:
 
     def _step(self, w: _Warp) -> bool:
         """Advance warp ``w`` by one phase if it can; returns whether anything happened."""
-        if w.ticket is None:
-            return self._draw(w)
         r = w.rank
+        if w.ticket is None:
+            if w.nxt is not None:                              # the look-ahead ticket becomes the current tile
+                w.ticket, w.nxt, w.phase, w.looked = w.nxt, None, (2 if w.pre else 0), False
+                w.pre = False
+                return True
+            t = self._draw_ticket(r)
+            if t is None:
+                return False
+            w.ticket, w.phase, w.looked = t, 0, False
+            return True
         k, c, s = w.ticket
         C = self.chunks
         tag = self._tag(k // self.sweeps)
+        if self.lookahead and not w.looked:                    # grab() of the next ticket, before anything else
+            w.looked = True
+            w.nxt = self._draw_ticket(r, transition=False)
+            return True
+        if (self.prefetch and self.sync == "dataflow" and w.nxt is not None and not w.pre and 2 <= w.phase <= 4
+                and self.rng.random() < 0.5 and (self.prefetch_ghost or not self._reads_ghost(r, w.nxt))
+                and self._deps_ready(r, w.nxt, local_only=True)):
+            # tail of the row loop: the probe found the next tile's nine completion words set -> its loads are issued
+            self._read(r, w.nxt)
+            w.pre = True
+            return True
         if w.phase == 0:
-            if not self._deps_ready(w):
+            if not self._deps_ready(r, w.ticket):
                 return False
             w.phase = 1
         elif w.phase == 1:
-            self._read(w)
+            self._read(r, w.ticket)
             w.phase = 2
         elif w.phase == 2:
             self.version[r][(k + 1) & 1][c][s] = tag + k + 1

@@ -98,3 +98,22 @@ def test_random_geometries_property():
               flags=combo[0], sync=combo[1], seed=seed, stall_rate=0.05, max_stall=200).run()
 
     run()
+
+
+def test_prefetch_must_skip_tiles_that_read_ghost_rows():
+    """The next-tile prefetch probes the nine LOCAL completion words only, so the kernel never prefetches a tile that
+    reads ghost rows (stencil2d_fused.cu: NextTile.valid); the model shows what happens otherwise."""
+    kw = dict(ranks=3, chunks=3, strips=4, sweeps=5, warps=3)
+    assert explore(seeds=80, **kw)["violations"] == 0                       # look-ahead + prefetch as built
+    assert explore(seeds=80, lookahead=False, prefetch=False, **kw)["violations"] == 0
+    bad = explore(seeds=80, prefetch_ghost=True, **kw)
+    assert bad["violations"] > 0 and "ghost" in bad["first"]
+
+
+def test_lookahead_tickets_do_not_deadlock():
+    """A warp holds its next ticket while it runs the current one (grab() behind the tile).  The lowest unfinished
+    ticket is still always somebody's CURRENT tile, so it can run: no schedule may end in a deadlock (Model.run raises
+    RuntimeError on one), also with a single warp per rank and more tiles than warps."""
+    for warps in (1, 2, 7):
+        for seed in range(25):
+            Model(ranks=3, chunks=4, strips=3, sweeps=4, warps=warps, launches=2, seed=seed).run()
