@@ -312,7 +312,9 @@ if __name__ == "__main__":                                 # python -m mpi_cuda_
     ap.add_argument("--sync", choices=["dataflow", "barrier"], default="dataflow")
     ap.add_argument("--no-drain", action="store_true")
     ap.add_argument("--no-upload", action="store_true")
+    ap.add_argument("--no-prefetch", action="store_true")
+    ap.add_argument("--prefetch-ghost", action="store_true", help="the unsound variant the kernel avoids")
     a = ap.parse_args()
     print(json.dumps(explore(a.seeds, ranks=a.ranks, chunks=a.chunks, strips=a.strips, sweeps=a.sweeps, warps=a.warps,
                              launches=a.launches, flags=a.flags, sync=a.sync, drain=not a.no_drain,
-                             upload=not a.no_upload)))
+                             upload=not a.no_upload, prefetch=not a.no_prefetch, prefetch_ghost=a.prefetch_ghost)))
