@@ -8,7 +8,6 @@ print_array (kernel.cu:115-129); the reference times nothing.
     python benchmarks/microbench.py [--n 16384] [--log gpurun_out/microbench.jsonl]
 """
 import argparse
-import ctypes as C
 import os
 import statistics
 import sys

@@ -7,7 +7,6 @@ import os
 import re
 import subprocess
 
-import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "mcp_b200.h")
