@@ -38,6 +38,8 @@ class _Warp:
     nxt: Optional[Tuple[int, int, int]] = None       # look-ahead ticket, drawn when the current tile starts
     looked: bool = False                             # the look-ahead draw of the current tile has been attempted
     pre: bool = False                                # the look-ahead tile's input has been read already (prefetch)
+    early_step: int = 0                              # early_up_signal: 0 = push pending, 1 = signal pending
+    early_done: bool = False                         # early_up_signal: this tile has already pushed + signalled upwards
 
 
 @dataclass
@@ -55,6 +57,8 @@ class Model:
     lookahead: bool = True        # a warp draws its next ticket when it starts a tile (grab() behind the current tile)
     prefetch: bool = True         # ... and reads that tile's input early if a non-blocking probe finds it settled
     prefetch_ghost: bool = False  # UNSOUND variant: prefetch also tiles that read ghost rows, probing tile_done only
+    early_up_signal: bool = False  # PROPOSED variant (not in the kernel): a top boundary tile pushes and signals its
+    #                                first rows upwards as soon as they exist, before it computes the rest of the tile
     seed: int = 0
     stall_rate: float = 0.02      # probability per scheduler round that the adversary freezes a warp or a rank
     max_stall: int = 400          # longest freeze, in scheduler rounds
@@ -217,21 +221,34 @@ class Model:
             self._read(r, w.ticket)
             w.phase = 2
         elif w.phase == 2:
+            early = self.early_up_signal and c == 0 and self._has(r, 0) and not w.early_done
+            if early:
+                # the rows streamed first are the upper ghost rows (all read by now) and the tile's top rows: push them
+                # and raise the upper neighbour's flag, then go on with the rest of the tile (two scheduler steps)
+                if w.early_step == 0:
+                    self.ghost[r - 1][(k + 1) & 1][1][s] = tag + k + 1
+                    w.early_step = 1
+                else:
+                    self.strip_flag[r - 1][1][s] = k + 1
+                    self.counter[r - 1][1] += 1
+                    w.early_step, w.early_done = 0, True
+                return True
             self.version[r][(k + 1) & 1][c][s] = tag + k + 1
             w.phase = 3
         elif w.phase == 3:                                     # halo push into the neighbours' ghost rows
-            if c == 0 and self._has(r, 0):
+            if c == 0 and self._has(r, 0) and not w.early_done:
                 self.ghost[r - 1][(k + 1) & 1][1][s] = tag + k + 1
             if c == C - 1 and self._has(r, 1):
                 self.ghost[r + 1][(k + 1) & 1][0][s] = tag + k + 1
             w.phase = 4
         elif w.phase == 4:                                     # signals behind the fence
-            if c == 0 and self._has(r, 0):
+            if c == 0 and self._has(r, 0) and not w.early_done:
                 self.strip_flag[r - 1][1][s] = k + 1
                 self.counter[r - 1][1] += 1
             if c == C - 1 and self._has(r, 1):
                 self.strip_flag[r + 1][0][s] = k + 1
                 self.counter[r + 1][0] += 1
+            w.early_done = False
             w.phase = 5
         else:
             self.tile_done[r][c][s] = k + 1

@@ -117,3 +117,14 @@ def test_lookahead_tickets_do_not_deadlock():
     for warps in (1, 2, 7):
         for seed in range(25):
             Model(ranks=3, chunks=4, strips=3, sweeps=4, warps=warps, launches=2, seed=seed).run()
+
+
+def test_proposed_early_upward_signal_is_sound():
+    """Design check for an optimisation that is NOT in the kernel yet (NOTES_NEXT_ROUND.md): a top boundary tile pushes
+    its first rows upwards and raises the neighbour's flag as soon as they exist -- by then it has consumed its upper
+    ghost rows, which are the first rows it streams -- and only then computes the rest of the tile.  The neighbour's
+    wait ends most of a tile earlier; the model finds no hazard, also with one chunk per rank and across launches."""
+    for kw in (dict(ranks=3, chunks=3, strips=4, sweeps=5, warps=3), dict(ranks=4, chunks=1, strips=3, sweeps=4, warps=2),
+               dict(ranks=3, chunks=2, strips=4, sweeps=4, warps=3, launches=3)):
+        r = explore(seeds=80, early_up_signal=True, **kw)
+        assert r["violations"] == 0, r.get("first")
