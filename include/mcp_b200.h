@@ -17,6 +17,14 @@
 extern "C" {
 #endif
 
+/* return codes (also what mcp_fused2d_status / mcp_fused3d_status and the result blocks carry) */
+#define MCP_OK 0
+#define MCP_ERR_CUDA (-1)        /* a CUDA runtime / driver call failed; mcp_last_error() has its message */
+#define MCP_ERR_ARG (-2)         /* an argument or descriptor was refused before anything was launched */
+#define MCP_ERR_UNSUPPORTED (-3) /* no kernel instantiation for this operator / dtype / time block */
+#define MCP_ERR_TIMEOUT (-4)     /* an in-kernel flag, barrier or TMA wait ran into MCP_OPT_TIMEOUT_MS */
+#define MCP_ERR_STATE (-5)       /* the object is not in a state that allows the call */
+
 /* element kinds */
 #define MCP_DTYPE_F32 0
 #define MCP_DTYPE_F64 1

@@ -8,12 +8,7 @@
 #include <stdio.h>
 #include <string.h>
 
-#define MCP_OK 0
-#define MCP_ERR_CUDA -1
-#define MCP_ERR_ARG -2
-#define MCP_ERR_UNSUPPORTED -3
-#define MCP_ERR_TIMEOUT -4
-#define MCP_ERR_STATE -5
+#include "../../../include/mcp_b200.h"  // MCP_OK, MCP_ERR_* (the public return codes)
 
 namespace mcp {
 
