@@ -52,3 +52,18 @@ def test_c_example_uses_only_declared_functions():
     used = set(re.findall(r"\b(mcp_[a-z0-9_]+)\s*\(", src))
     assert used and used <= _declared()
     assert len(C_HOST_ONLY & used) >= 3      # the reason those exist
+
+
+def test_header_is_strict_c99_and_cxx11_and_defines_the_return_codes(tmp_path):
+    """A host in plain C must be able to include the header on its own and name every return code."""
+    body = ('#include "mcp_b200.h"\n'
+            "int main(void) { int codes[] = {MCP_OK, MCP_ERR_CUDA, MCP_ERR_ARG, MCP_ERR_UNSUPPORTED, MCP_ERR_TIMEOUT,\n"
+            "                                MCP_ERR_STATE, MCP_STOP_SLOT_LIMIT, MCP_OPT_TIMEOUT_MS, MCP_RES_FINAL};\n"
+            "  return (int)(sizeof(codes) / sizeof(codes[0])) == 9 && sizeof(mcp_fused2d_desc) > 0 ? 0 : 1; }\n")
+    inc = os.path.join(ROOT, "include")
+    for name, cc, std in (("h.c", "gcc", "-std=c99"), ("h.cpp", "g++", "-std=c++11")):
+        src = tmp_path / name
+        src.write_text(body)
+        r = subprocess.run([cc, std, "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", inc, "-c", str(src),
+                            "-o", str(tmp_path / (name + ".o"))], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
