@@ -34,7 +34,7 @@ with Solver(cfg) as s:
     if s.ctx.rank == 0:
         mid = field[a.size // 2, a.size // 2]
         print(f"{a.size} x {a.size} {a.dtype} on {s.ctx.world} rank(s) [{s.backend}]: {st.generations} generations, "
-              f"{st.launches} launch(es), stop: {st.stop_reason or 'tolerance loop'}, last max|du| = "
+              f"{st.launches} launch(es), stop: {st.stop_reason}, last max|du| = "
               f"{st.residual_history[-1][1]:.3e}, centre = {mid:.4f}, {st.glups:.1f} GLUPS")
         if a.out:
             import numpy as np

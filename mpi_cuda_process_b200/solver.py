@@ -929,7 +929,10 @@ class Solver:
             r = float(np.sqrt(ss)) if kind == "l2" else mx
             total.residual_history.append((self.generation, r))
             if r <= tol:
+                total.stop_reason = "converged"
                 break
+        if not total.stop_reason:
+            total.stop_reason = "max_generations"
         return total
 
     def _run_to_tolerance_fused(self, tol: float, max_g: int, kind: str) -> RunStats:

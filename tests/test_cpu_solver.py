@@ -122,6 +122,10 @@ def test_run_to_tolerance_cpu():
         st = s.run_to_tolerance()
         assert st.residual_history[-1][1] <= 1e-2
         assert s.generation < 2000 and s.generation % 10 == 0
+        assert st.stop_reason == "converged"
+    with Solver(RunConfig(workload="mdf", height=12, width=12, backend="cpu", tol=1e-9, max_generations=20)) as s:
+        s.initialize()
+        assert s.run_to_tolerance().stop_reason == "max_generations"
 
 
 def test_checksum_is_decomposition_independent():
