@@ -213,11 +213,12 @@ def main(argv: Optional[List[str]] = None) -> int:
                 "generations": stats.generations, "device_ms": round(stats.device_ms, 4),
                 "glups": round(stats.glups, 3), "launches": stats.launches,
                 "residual": stats.residual_history[-1][1] if stats.residual_history else None,
+                "stop_reason": stats.stop_reason or None,
             }
             if args.log_jsonl:
                 from .utils.log import JsonlLogger
                 lg = JsonlLogger(args.log_jsonl, rank=ctx.rank)
-                lg.log(**summary, residual_history=stats.residual_history[-64:], stop_reason=stats.stop_reason)
+                lg.log(**summary, residual_history=stats.residual_history[-64:])
                 lg.close()
             if args.json:
                 print(json.dumps(summary))
