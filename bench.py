@@ -16,7 +16,8 @@ and a device -> host read of the step's result (kernel status + global residual 
 step; ``e2e_with_gather`` additionally assembles the solution field on rank 0 (fused gather + pack over NVLink) and
 copies it to pinned host memory every step.  Each rank binds itself to the CPUs next to its GPU first (so that pinned
 buffers come from the GPU's memory node; ``--no-numa-bind`` switches that off; recorded under ``config``).
-``--impl reference`` is the reference arm (the reference cannot be built or run here).
+``--impl reference`` is the reference arm (see DESIGN.md: the reference cannot be built or run here);
+``--impl ref-fixed`` runs the patched reference program of ``baseline/`` (a baseline, not the reference arm).
 """
 from __future__ import annotations
 
@@ -39,7 +40,7 @@ def parse_args(argv=None):
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=10)
     p.add_argument("--warmup", type=int, default=3)
-    p.add_argument("--impl", default="fused", choices=["fused", "ours", "reference", "nccl", "staged"])
+    p.add_argument("--impl", default="fused", choices=["fused", "ours", "reference", "ref-fixed", "nccl", "staged"])
     p.add_argument("--workload", default="mdf", choices=["mdf", "life", "heat3d"],
                    help="mdf = the headline config; heat3d/life for the other BASELINE.json configs")
     p.add_argument("--depth", type=int, default=0)
@@ -76,6 +77,32 @@ def reference_arm(args) -> int:
     return 0
 
 
+def ref_fixed_arm(args) -> int:
+    """``--impl ref-fixed``: the reference's own MDF program with baseline/ref_fixed.patch applied, started as N ranks on
+    the MPI stand-in (NOT the unmodified reference, hence not ``--impl reference``).  It moves the whole grid over PCIe
+    three times per generation, so a handful of generations is all that is timed; GLUPS is still a rate."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0                      # the stand-in launcher starts the ranks itself
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import run_ref_fixed
+    gens = max(2, min(args.gens_per_step, 3))
+    h = args.height * (args.gpus if args.scaling == "weak" else 1)
+    try:
+        rec = run_ref_fixed.run(args.gpus, gens, h, args.width)
+    except Exception as e:            # no GPU, no reference tree to patch, ...: say so in one line
+        print(json.dumps({"impl": "ref-fixed", "unavailable": str(e).strip().splitlines()[0][:300], "metric": METRIC,
+                          "n_gpus": args.gpus}))
+        return 0
+    print(json.dumps({"metric": METRIC, "value": round(rec["glups"] , 4), "unit": "GLUPS", "n_gpus": args.gpus,
+                      "impl": "ref-fixed", "higher_is_better": True, "scaling": args.scaling, "dtype": "fp32",
+                      "data": "synthetic", "steps": 1, "warmup": 0, "ms_per_step": round(rec["seconds"] * 1e3, 3),
+                      "config": {"model": "2-D 5-point MDF (heat/Jacobi), Dirichlet ring=100", "grid": rec["grid"],
+                                 "generations": gens, "pattern": rec["pattern"]},
+                      "note": "wall clock between barriers inside the program (it has no device timing); "
+                              "baseline only, see BASELINE.md section 3"}))
+    return 0
+
+
 def maybe_respawn(args) -> None:
     """``python bench.py --gpus N`` without torchrun: start the N ranks ourselves."""
     if args.gpus > 1 and "RANK" not in os.environ:
@@ -89,6 +116,8 @@ def main(argv=None) -> int:
     args = parse_args(argv)
     if args.impl == "reference":
         return reference_arm(args)
+    if args.impl == "ref-fixed":
+        return ref_fixed_arm(args)
     maybe_respawn(args)
 
     import torch
