@@ -100,9 +100,9 @@ def resource_usage():
         rows.append((name, get("REG"), get("STACK"), get("SHARED"), get("LOCAL"), get(r"CONSTANT\[0\]")))
     rows.sort()
     with open(os.path.join(OUT, "resource_usage.txt"), "w") as f:
-        f.write("# cuobjdump --dump-resource-usage of libmcp_b200.so (sm_100a, -lineinfo).  STACK = 8 is the call frame of "
-                "the\n# __noinline__ wait helpers; larger values are register spills (ptxas -v figures: "
-                "ptxas_stencil2d_fused.txt).\n# Dynamic shared memory (TMA rings) is set at launch and not listed.\n")
+        f.write("# cuobjdump --dump-resource-usage of libmcp_b200.so (sm_100a, -lineinfo).  STACK is the call frame of "
+                "the\n# __noinline__ wait helpers (8 bytes) and/or register spills (ptxas -v figures: "
+                "ptxas_spills.txt).\n# Dynamic shared memory (TMA rings) is set at launch and not listed.\n")
         f.write(f"{'REG':>4} {'STACK':>6} {'SMEM':>6} {'LOCAL':>6} {'CONST0':>7}  kernel\n")
         for n, r, st, sh, lo, c in rows:
             f.write(f"{r:>4} {st:>6} {sh:>6} {lo:>6} {c:>7}  {n}\n")
@@ -112,9 +112,10 @@ def resource_usage():
 rows = resource_usage()
 index.append("")
 index.append(f"`resource_usage.txt`: registers, stack, static shared and local memory of all {len(rows)} kernels in the "
-             f"library (`cuobjdump --dump-resource-usage`); `ptxas_stencil2d_fused.txt`: the `ptxas -v` figures of the "
+             f"library (`cuobjdump --dump-resource-usage`); `ptxas_spills.txt`: the `ptxas -v` figures of the "
              f"sweep kernels.  The 8-warp time-block-8 kernels (up to {max(r[1] for r in rows)} registers) do not spill; "
              f"{sum(1 for r in rows if r[2] > 8)} of the 16-warp instantiations at the 128-register cap spill 16-228 "
-             f"bytes (time block 4: fp64, packed fp32, the emulated-ranks kernel; life int32 TB = 2 with residual).")
+             f"bytes (time block 4: fp64, packed fp32, the emulated-ranks kernel; life int32 TB = 2 with residual), and "
+             f"so does the fp64 residual instantiation of the 3-D kernel (16 bytes).")
 open(os.path.join(OUT, "README.md"), "w").write("\n".join(index) + "\n")
 print("\n".join(index[4:]))
